@@ -1,0 +1,195 @@
+/*
+ * hrt.h — C ABI of the B200-native path-tracing core that replaces the CPU render loop of
+ * Todegal/HobbyRaytracer.
+ *
+ * The reference has no FFI / plugin interface: its seam is the free function
+ *   static void render(int nThreads, shared_ptr<Texture> background, shared_ptr<Hittable> world,
+ *                      const Camera& camera, shared_ptr<Film>& film)        (hobbyraytracer/main.cpp:81-140)
+ * called once from main() (main.cpp:176), fed by objects that Scene::loadScene constructs
+ * (scene.cpp:127-374).  All geometry/material fields of those objects are private, so the scene crosses
+ * this boundary as a *builder*: every hrt_scene_add_* call below corresponds to one std::make_shared<X>(...)
+ * construction site of the reference and takes exactly the constructor arguments of X.
+ *
+ * Conventions: plain pointers and sizes only; every int-returning function returns >= 0 on success
+ * (an id where documented) and < 0 on error, with the message available from hrt_last_error().
+ * Nothing throws across the ABI.  Host pointers are only read during the call that takes them.
+ * The library is CUDA-only: there is no CPU fallback; without a usable sm_100 device every compute
+ * entry point fails with HRT_ERR_CUDA.
+ *
+ * The same builder signatures (with the prefix orc_ / ref_ instead of hrt_) are implemented by the CPU
+ * oracle (oracle/oracle.cpp) and by the harness that drives the unmodified reference (oracle/ref_harness.cpp),
+ * so parity tests feed the identical scene to all three.
+ */
+#ifndef HRT_H
+#define HRT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HRT_ABI_VERSION 1
+
+/* ---- error codes --------------------------------------------------------------------------- */
+#define HRT_OK            0
+#define HRT_ERR_ARG      -1   /* bad argument / id out of range                                   */
+#define HRT_ERR_STATE    -2   /* call not valid in this state (e.g. render before commit)          */
+#define HRT_ERR_CUDA     -3   /* CUDA runtime failure (no device, OOM, launch error)               */
+#define HRT_ERR_IO       -4   /* file could not be read / written / parsed                         */
+
+#define HRT_MISS 0xFFFFFFFFu  /* primitive id reported for a ray that hit nothing                  */
+
+/* ---- material kinds: Material subclasses of material.h ------------------------------------- */
+enum {
+    HRT_MAT_LAMBERTIAN    = 0,  /* Lambertian(albedo)                         material.h:132-157 */
+    HRT_MAT_METAL         = 1,  /* Metal(albedo, roughness=p0)                material.h:159-182 */
+    HRT_MAT_DIELECTRIC    = 2,  /* Dielectric(ior=p0, roughness=p1)           material.h:199-242 */
+    HRT_MAT_ISOTROPIC     = 3,  /* Isotropic(albedo)                          material.h:73-89   */
+    HRT_MAT_DIFFUSE_LIGHT = 4,  /* DiffuseLight(colour=albedo, strength=p0)   material.h:91-109  */
+    HRT_MAT_PBR           = 5,  /* PBR(albedo, metalness=p1, roughness=p0)    material.cpp:4-28  */
+    HRT_MAT_UVTEST        = 6   /* UVTest()                                   material.h:111-130 */
+};
+
+/* MatVec3 / MatScalar (material.h:10-58): a constant, or a texture when the *_tex id is >= 0.   */
+typedef struct hrt_material {
+    int32_t kind;
+    float   albedo[3];
+    int32_t albedo_tex;   /* -1 = use albedo[]                                                    */
+    float   p0;
+    int32_t p0_tex;       /* -1 = use p0; scalar-from-texture = length(rgb) (material.h:49-51)    */
+    float   p1;
+    int32_t p1_tex;
+} hrt_material;
+
+/* ---- instance wrappers: translate.h / scale.h / rotateQuat.h / rotateY.h ------------------- */
+enum {
+    HRT_XF_TRANSLATE   = 0,   /* v = offset xyz                        translate.cpp:7-19          */
+    HRT_XF_SCALE       = 1,   /* v = factor xyz                        scale.cpp:11-27             */
+    HRT_XF_ROTATE_QUAT = 2,   /* v = quaternion (w, x, y, z)           rotateQuat.cpp:44-66        */
+    HRT_XF_ROTATE_Y    = 3,   /* v = (sinTheta, cosTheta, -, -)        rotateY.cpp:44-75           */
+    HRT_XF_ROTATE_EULER_DEG = 4, /* v = Euler degrees xyz; converted on the host exactly like
+                                    glm::quat(glm::radians(angles)) (scene.cpp:340) into ROTATE_QUAT */
+    HRT_XF_ROTATE_Y_DEG = 5   /* v = (degrees); converted like RotateY's ctor (rotateY.cpp:7-9)    */
+};
+typedef struct hrt_xform {
+    int32_t kind;
+    float   v[4];
+} hrt_xform;
+
+/* Camera(lookFrom, lookAt, up, vfov, aspectRatio, aperture, focusDistance)   camera.h:9-30         */
+typedef struct hrt_camera {
+    float position[3];
+    float look_at[3];
+    float up[3];
+    float vfov_deg;
+    float aspect;          /* Film::getAspectRatio() = float(w)/float(h)   film.h:20-22             */
+    float aperture;        /* parsed but unused by the reference (camera.h:34-35)                   */
+    float focal_distance;
+} hrt_camera;
+
+/* BVH flavours for hrt_scene_commit */
+enum {
+    HRT_BVH_REFERENCE = 0,  /* bvh.cpp:6-61 topology (median split on a pseudo-random axis, leaves of 1-2),
+                               flat world list, fixed left-then-right order: reproduces the reference's
+                               visiting order, hence its tie-breaking, exactly                      */
+    HRT_BVH_SAH       = 1,  /* binned-SAH BVH over each mesh + top-level BVH over world objects, built on host */
+    HRT_BVH_LBVH_GPU  = 2   /* Morton-code LBVH built on the GPU (same node format as SAH)          */
+};
+
+typedef struct hrt_render_params {
+    int32_t  width, height;
+    int32_t  spp;            /* film.samples: divisor of the per-pixel mean (main.cpp:126)          */
+    int32_t  sample_first;   /* this call renders sample indices [sample_first, sample_first+sample_count) */
+    int32_t  sample_count;   /* <= 0 means "all spp"                                                 */
+    int32_t  max_depth;      /* MAX_DEPTH = 50 (main.cpp:32); <= 0 selects 50                        */
+    float    t_min;          /* 0.001f (main.cpp:45); <= 0 selects 0.001f                            */
+    uint64_t seed;           /* Philox key; the image depends only on (seed, pixel, sample index)    */
+    int32_t  rng_mode;       /* 0 = reference-distribution (glm/rand() byte quirk, random.inl:19-27), 1 = plain uniform */
+    int32_t  flags;          /* HRT_RENDER_* bits                                                    */
+} hrt_render_params;
+
+#define HRT_RENDER_MEGAKERNEL 1   /* one thread per path instead of the wavefront pipeline (debug/validation) */
+
+typedef struct hrt_stats {
+    uint64_t rays;            /* closest-hit queries issued (= world->hit calls of main.cpp:45)      */
+    uint64_t paths;           /* camera samples                                                      */
+    uint64_t launches;        /* kernel launches of this library since the last reset                */
+    double   ms_trace;        /* device time in the traversal kernel (CUDA events)                   */
+    double   ms_shade;        /* device time in the shading / regeneration kernel                    */
+    double   ms_other;        /* raygen, film, resets                                                */
+    double   ms_total;        /* device time of the whole call                                       */
+    uint64_t node_tests;      /* only filled by counters-enabled entry points                        */
+    uint64_t prim_tests;
+} hrt_stats;
+
+typedef struct hrt_scene hrt_scene;
+
+/* ---- library ------------------------------------------------------------------------------- */
+int         hrt_abi_version(void);
+const char* hrt_last_error(void);                /* thread-local, never NULL                         */
+int         hrt_device_count(void);              /* number of usable CUDA devices, < 0 on failure    */
+int         hrt_set_device(int device);          /* device used by scenes created afterwards         */
+
+/* ---- scene builder (one call per construction site of scene.cpp) ---------------------------- */
+hrt_scene*  hrt_scene_create(void);
+void        hrt_scene_destroy(hrt_scene* s);
+
+int hrt_scene_add_texture_solid(hrt_scene* s, const float rgb[3]);                    /* texture.h:9-25    */
+int hrt_scene_add_texture_checker(hrt_scene* s, int even_tex, int odd_tex);          /* texture.cpp:17-28 */
+int hrt_scene_add_texture_image(hrt_scene* s, const uint8_t* rgb8, int w, int h);    /* texture.cpp:53-74; w*h*3 bytes; w==0 -> cyan */
+int hrt_scene_add_texture_env(hrt_scene* s, const float* data, int w, int h, int channels); /* texture.cpp:76-97 */
+int hrt_scene_add_material(hrt_scene* s, const hrt_material* m);
+
+/* shapes: return a shape id.  Primitive ids of a shape are hrt_scene_prim_base(shape) + local index. */
+int hrt_scene_add_sphere(hrt_scene* s, const float center[3], float radius, int material);        /* sphere.h:9      */
+int hrt_scene_add_rect(hrt_scene* s, int axis, float a0, float a1, float b0, float b1, float k, int material);
+      /* axis 0: YZRect(y0,y1,z0,z1,k)  1: XZRect(x0,x1,z0,z1,k)  2: XYRect(x0,x1,y0,y1,k)      aarect.h          */
+int hrt_scene_add_box(hrt_scene* s, const float center[3], const float dimensions[3], int material); /* box.h:41-44; 6 prims in box.h:31-38 order */
+int hrt_scene_add_mesh(hrt_scene* s, const float* positions /* n_tri*9 */, const float* normals /* n_tri*9 or NULL */,
+                       const float* uvs /* n_tri*6 or NULL */, int64_t n_tri, int material);       /* mesh.cpp:13-41: one ITriangle per face + BVH */
+int64_t hrt_scene_prim_base(const hrt_scene* s, int shape);
+int64_t hrt_scene_prim_count(const hrt_scene* s);
+
+/* world list entries, in order (scene.cpp:356 objects.add).  ops are listed innermost first, i.e. in the
+ * order the loader wraps them (rotate, scale, translate; scene.cpp:335-353). */
+int hrt_scene_add_object(hrt_scene* s, int shape, const hrt_xform* ops, int n_ops);
+/* ConstantMedium(boundary = wrapped shape, density, albedo)  constantMedium.h:10-14.  albedo_tex < 0 -> rgb.
+ * The medium is one primitive (its id = hrt_scene_prim_base of the returned pseudo-shape id). */
+int hrt_scene_add_medium(hrt_scene* s, int shape, const hrt_xform* ops, int n_ops, float density,
+                         const float rgb[3], int albedo_tex);
+int hrt_scene_set_background(hrt_scene* s, int texture);                                           /* scene.cpp:215-237 */
+
+/* Upload + build acceleration structures.  seed drives the split-axis stream of HRT_BVH_REFERENCE. */
+int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed);
+
+/* ---- hot path ------------------------------------------------------------------------------ */
+/* Closest-hit on a ray batch: world->hit(r, t_min, t_max, rec) of main.cpp:45 / hittableList.cpp:4-21.
+ * rays: n x 8 floats (ox,oy,oz,t_min, dx,dy,dz,t_max).  Outputs: primitive id (HRT_MISS on miss) and rec.t.
+ * optional outputs (may be NULL): normal n x 3 (rec.normal), uv n x 2, front n bytes (rec.frontFace).
+ * rng_seed only matters for scenes with media (their hit() draws a random number). */
+int hrt_trace_batch(hrt_scene* s, const float* rays, int64_t n, uint32_t* prim_id, float* t,
+                    float* normal, float* uv, uint8_t* front, uint64_t rng_seed);
+/* Same with device-resident buffers (inputs already in HBM); stream = cudaStream_t or NULL. */
+int hrt_trace_batch_device(hrt_scene* s, const void* d_rays, int64_t n, void* d_prim_id, void* d_t,
+                           uint64_t rng_seed, void* stream);
+
+/* render(): main.cpp:81-140.  out_sum: width*height*3 floats receiving the per-pixel *sum* of the rendered
+ * samples (NULL to skip); out_rgb8: width*height*3 bytes = Film::tonemap + writeColour of sum/spp
+ * (film.cpp:25-52), row 0 = top row as in the reference's pixel buffer (NULL to skip). */
+int hrt_render(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, float* out_sum, uint8_t* out_rgb8);
+/* Device variants for multi-GPU use: accumulate sample sums into a device buffer of width*height*3 floats
+ * (the caller zeroes it and may NCCL-reduce it), then resolve a summed buffer to 8-bit / mean. */
+int hrt_render_accumulate_device(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
+                                 void* d_accum, void* stream);
+int hrt_film_resolve_device(hrt_scene* s, const void* d_accum, int width, int height, int spp,
+                            void* d_mean_or_null, void* d_rgb8_or_null, void* stream);
+
+int hrt_get_stats(hrt_scene* s, hrt_stats* out);
+int hrt_reset_stats(hrt_scene* s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HRT_H */

@@ -1,0 +1,112 @@
+// hrt_host.h — host-side scene builder: collects the constructor calls of scene.cpp:127-374 / mesh.cpp:13-41 and
+// flattens them into the arrays of hrt_types.h.  No CUDA in here (plain C++17).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "hrt_types.h"
+
+namespace hrt {
+
+struct HostTexture {
+    int kind = TEX_SOLID;
+    float rgb[3] = {0, 0, 0};
+    int even = -1, odd = -1;
+    int w = 0, h = 0, ch = 0;
+    std::vector<uint8_t> u8;
+    std::vector<float> f32;
+    std::vector<uint32_t> rgbe;     // filled at commit when every texel of an env map is exactly RGBE-representable
+    int rgbe_tried = 0;
+};
+
+struct RefBvh {                      // bvh.cpp:6-61 in index form
+    std::vector<float4> nodes;       // 2 per node
+    int root = -1;
+};
+struct FastBvh {
+    std::vector<float4> nodes;       // 4 per node
+    std::vector<int> order;          // leaf order -> item index
+    int root = -1;
+    int depth = 0;
+};
+
+struct HostShape {
+    int kind = SHAPE_SPHERE;
+    float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int axis = 0;
+    int material = -1;
+    std::vector<float> pos, nrm, uv;
+    int64_t n_tri = 0;
+    int64_t prim_base = 0, prim_count = 0;
+    bool used = false;
+    int mesh_index = -1;
+    RefBvh ref;
+    FastBvh fast;
+    std::vector<float4> tris4, attrs4;   // device layouts of hrt_types.h (DMesh::tris, DMesh::attrs)
+    std::vector<float4> leaves;          // DMesh::fast_leaves
+};
+
+struct HostObject {
+    int shape = -1;
+    std::vector<DXform> ops;         // innermost first
+    bool medium = false;
+    float neg_inv_density = 0;
+    int phase_tex = -1;
+    float phase_rgb[3] = {0, 0, 0};
+    int pseudo_shape = -1;
+};
+
+struct HostScene {
+    std::vector<HostTexture> textures;
+    std::vector<hrt_material> materials;
+    std::vector<HostShape> shapes;
+    std::vector<HostObject> objects;
+    int64_t n_prims = 0;
+    int background = -1;
+    bool committed = false;
+    int bvh_mode = HRT_BVH_REFERENCE;
+    // results of flatten()
+    std::vector<DObject> d_objects;
+    std::vector<DXform> d_xforms;
+    std::vector<int> mesh_shapes;    // DScene::meshes[i] is built from shapes[mesh_shapes[i]]
+    FastBvh tlas;
+    float tlas_cull_scale = 1.0f;
+    double build_ms_ref = 0, build_ms_fast = 0;
+};
+
+// Converts the ABI's hrt_xform (incl. the *_DEG conveniences) into the device record, with the host-side
+// trigonometry of scene.cpp:340 / rotateY.cpp:7-9.
+DXform make_xform(const hrt_xform& x);
+
+// bvh.cpp:6-61: median split of box.min[axis] with axis = glm::linearRand(0,2) on the stream (seed, shape_id).
+void build_ref_bvh(HostShape& sh, uint64_t seed, int shape_id, int n_threads);
+// Binned-SAH BVH2 over arbitrary boxes (used for meshes and for the top-level BVH).
+void build_fast_bvh(const std::vector<float>& bmin, const std::vector<float>& bmax, FastBvh& out, int n_threads);
+void triangle_boxes(const HostShape& sh, std::vector<float>& bmin, std::vector<float>& bmax);   // triangle.cpp:133-151
+
+// Fills d_objects / d_xforms / tlas; builds the per-mesh BVHs.  Returns "" or an error message.
+std::string flatten(HostScene& s, int bvh_mode, uint64_t seed);
+
+// Exact-repack test for environment maps: true (and rgbe filled) when every texel equals ldexp(m, e - 136) with
+// 8-bit mantissas and one shared exponent, which is what stb_image produces for Radiance .hdr files (texture.cpp:99-115).
+bool try_pack_rgbe(const std::vector<float>& f32, int w, int h, int ch, std::vector<uint32_t>& rgbe);
+
+// Camera ctor camera.h:9-30
+DCamera make_camera(const hrt_camera& c);
+
+// scene-builder half of the C ABI (hrt_builder.cpp): ids >= 0 or HRT_ERR_* with `err` filled
+int b_add_texture_solid(HostScene& s, const float rgb[3], std::string& err);
+int b_add_texture_checker(HostScene& s, int even_tex, int odd_tex, std::string& err);
+int b_add_texture_image(HostScene& s, const uint8_t* rgb8, int w, int h, std::string& err);
+int b_add_texture_env(HostScene& s, const float* data, int w, int h, int channels, std::string& err);
+int b_add_material(HostScene& s, const hrt_material* m, std::string& err);
+int b_add_sphere(HostScene& s, const float c[3], float radius, int material, std::string& err);
+int b_add_rect(HostScene& s, int axis, float a0, float a1, float b0, float b1, float k, int material, std::string& err);
+int b_add_box(HostScene& s, const float c[3], const float dim[3], int material, std::string& err);
+int b_add_mesh(HostScene& s, const float* pos, const float* nrm, const float* uv, int64_t n_tri, int material, std::string& err);
+int b_add_object(HostScene& s, int shape, const hrt_xform* ops, int n_ops, std::string& err);
+int b_add_medium(HostScene& s, int shape, const hrt_xform* ops, int n_ops, float density, const float rgb[3], int albedo_tex, std::string& err);
+int b_set_background(HostScene& s, int tex, std::string& err);
+
+} // namespace hrt

@@ -1,0 +1,92 @@
+// hrt_types.h — plain-old-data records shared by the host flattener (hrt_host.cpp) and the CUDA kernels
+// (hrt_kernels.cu).  The reference's pointer tree (Hittable / Material / Texture, hittable.h:27-32,
+// material.h:60-71, texture.h:3-7) becomes these GPU-resident arrays.
+#pragma once
+#include <stdint.h>
+#include <vector_types.h>
+
+#include "../../include/hrt.h"
+
+namespace hrt {
+
+constexpr int MAX_XF = 8;                    // instance wrappers per world-list entry
+constexpr int MAT_MEDIUM_BASE = 1 << 24;     // material id >= this: Isotropic phase function of object (id - base)
+constexpr int REF_STACK = 64;                // reference topology is balanced: depth <= ceil(log2 n) + 1
+constexpr int FAST_STACK = 96;               // SAH tree depth cap (FAST_MAX_DEPTH) + top-level tree + markers
+constexpr int FAST_MAX_DEPTH = 60;
+
+enum { SHAPE_SPHERE = 0, SHAPE_RECT = 1, SHAPE_BOX = 2, SHAPE_MESH = 3, SHAPE_MEDIUM = 4 };
+enum { TEX_SOLID = 0, TEX_CHECKER = 1, TEX_IMAGE = 2, TEX_ENV = 3, TEX_ENV_RGBE = 4 };
+
+// translate.h / scale.h: (a,b,c) = vector.  rotateQuat.h: (a,b,c,d) = (w,x,y,z).  rotateY.h: a = sin, b = cos.
+struct DXform { int kind; float a, b, c, d; };
+
+// One world-list entry (scene.cpp:356 objects.add) = a shape under its wrapper chain, optionally a ConstantMedium.
+struct DObject {
+    int kind;               // SHAPE_* of the wrapped shape
+    int axis;               // rects
+    int material;
+    uint32_t prim_base;     // primitive id of the first primitive of the shape
+    uint32_t medium_prim;   // media: the pseudo primitive id reported for a hit inside the volume
+    int mesh;               // index into DScene::meshes
+    int xf_first, xf_count; // chain in DScene::xforms, innermost first (scene.cpp:335-353 wrap order)
+    int medium;             // 1: ConstantMedium(boundary = this wrapped shape)   constantMedium.h:10-14
+    int has_quat;           // chain contains a RotateQuat (its hit() reports t in other units, rotateQuat.cpp:51)
+    float f[8];             // sphere: centre, radius | rect: a0 a1 b0 b1 k | box: min xyz, max xyz (box.h:41-44)
+    float neg_inv_density;
+    int phase_tex;
+    float phase_rgb[3];
+};
+
+// Mesh (mesh.cpp:13-41): triangles + two acceleration structures.
+//  ref_nodes  : the reference's topology (bvh.cpp:6-61) — 2 x float4 per node: (min.xyz, left) (max.xyz, right);
+//               child >= 0 is a node, child < 0 is triangle ~child.  Traversed left-then-right (bvh.cpp:69-78).
+//  tris       : 3 x float4 per triangle in input order: (p0, -) (p1, -) (p2, -)
+//  attrs      : 4 x float4 per triangle in input order: (n0, uv0.x) (n1, uv0.y) (n2, uv1.x) (uv1.y, uv2.x, uv2.y, -)
+//  fast_leaves: one 128-byte record per BOTTOM node of the reference topology (a node whose children are triangles),
+//               8 x float4: (min.xyz, triL) (max.xyz, triR) (L.p0) (L.p1) (L.p2) (R.p0) (R.p1) (R.p2).  The box is
+//               the reference node's box, tested with the reference's own slab arithmetic, so which triangles a
+//               ray gets to test below t_min (ITriangle::hit ignores t_min, triangle.cpp:57-131) is unchanged.
+//  fast_nodes : binned-SAH BVH2 over those bottom nodes — 4 x float4 per node: (c0.lo.x c0.hi.x c0.lo.y c0.hi.y)
+//               (c1.lo.x c1.hi.x c1.lo.y c1.hi.y) (c0.lo.z c0.hi.z c1.lo.z c1.hi.z) (child0, child1, -, -);
+//               child >= 0 is a node, child < 0 is leaf record ~child.
+struct DMesh {
+    const float4* ref_nodes;
+    const float4* tris;
+    const float4* attrs;
+    const float4* fast_nodes;
+    const float4* fast_leaves;
+    int ref_root;           // -1: empty mesh
+    int fast_root;          // >= 0 node, < 0 leaf ~id; only valid when ref_root >= 0
+    int64_t n_tri;
+    uint32_t prim_base;
+    int material;
+};
+
+struct DTexture {
+    int kind;
+    float rgb[3];
+    int even, odd;
+    int w, h, ch;
+    const void* data;       // uint8 rgb (image), float (env) or uint32 rgbe (env, lossless repack)
+};
+
+struct DScene {
+    const DObject* objects;
+    const DXform* xforms;
+    const DMesh* meshes;
+    const hrt_material* materials;
+    const DTexture* textures;
+    const float4* tlas_nodes;   // top-level BVH over world-list entries (same node format as fast_nodes), or null
+    int tlas_root;              // >= 0 node, < 0 leaf = object ~id
+    int n_objects;
+    int n_materials;
+    int n_textures;
+    int background;
+    int fast;                   // 0: reference visiting order everywhere; 1: SAH BVHs + reference-order re-trace of ambiguous rays
+    float tlas_cull_scale;      // lower bound of (reported t) / (world t * |d|) over RotateQuat objects; 0 if none
+};
+
+struct DCamera { float origin[3], llc[3], horiz[3], vert[3]; };   // camera.h:9-30
+
+} // namespace hrt

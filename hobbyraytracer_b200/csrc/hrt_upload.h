@@ -1,0 +1,59 @@
+// hrt_upload.h — turns a flattened HostScene into the DScene view the kernels read.  `Up::put(src, bytes)` returns
+// where the bytes live for the consumer: a cudaMalloc'ed copy in the product (hrt_api.cu), the host pointer itself
+// in the CPU simulation harness (tests/hostsim).
+#pragma once
+#include <vector>
+
+#include "hrt_host.h"
+
+namespace hrt {
+
+template <class Up>
+DScene make_dscene(HostScene& s, Up& up)
+{
+    DScene d{};
+    const bool fast = s.bvh_mode != HRT_BVH_REFERENCE;
+    std::vector<DMesh> meshes(s.mesh_shapes.size());
+    for (size_t i = 0; i < s.mesh_shapes.size(); ++i) {
+        HostShape& sh = s.shapes[(size_t)s.mesh_shapes[i]];
+        DMesh m{};
+        m.ref_nodes = (const float4*)up.put(sh.ref.nodes.data(), sh.ref.nodes.size() * sizeof(float4));
+        m.tris = (const float4*)up.put(sh.tris4.data(), sh.tris4.size() * sizeof(float4));
+        m.attrs = (const float4*)up.put(sh.attrs4.data(), sh.attrs4.size() * sizeof(float4));
+        m.fast_nodes = (const float4*)up.put(sh.fast.nodes.data(), sh.fast.nodes.size() * sizeof(float4));
+        m.fast_leaves = (const float4*)up.put(sh.leaves.data(), sh.leaves.size() * sizeof(float4));
+        m.ref_root = sh.ref.root; m.fast_root = sh.fast.root;
+        m.n_tri = sh.n_tri; m.prim_base = (uint32_t)sh.prim_base; m.material = sh.material;
+        meshes[i] = m;
+    }
+    std::vector<DTexture> tex(s.textures.size());
+    for (size_t i = 0; i < s.textures.size(); ++i) {
+        HostTexture& t = s.textures[i];
+        DTexture x{};
+        x.kind = t.kind; x.rgb[0] = t.rgb[0]; x.rgb[1] = t.rgb[1]; x.rgb[2] = t.rgb[2];
+        x.even = t.even; x.odd = t.odd; x.w = t.w; x.h = t.h; x.ch = t.ch; x.data = nullptr;
+        if (t.kind == TEX_IMAGE && !t.u8.empty()) x.data = up.put(t.u8.data(), t.u8.size());
+        if (t.kind == TEX_ENV && !t.f32.empty()) {
+            if (t.rgbe.empty() && t.rgbe_tried == 0) { t.rgbe_tried = 1; try_pack_rgbe(t.f32, t.w, t.h, t.ch, t.rgbe); }
+            if (!t.rgbe.empty()) { x.kind = TEX_ENV_RGBE; x.data = up.put(t.rgbe.data(), t.rgbe.size() * sizeof(uint32_t)); }
+            else x.data = up.put(t.f32.data(), t.f32.size() * sizeof(float));
+        }
+        tex[i] = x;
+    }
+    d.objects = (const DObject*)up.put(s.d_objects.data(), s.d_objects.size() * sizeof(DObject));
+    d.xforms = (const DXform*)up.put(s.d_xforms.data(), s.d_xforms.size() * sizeof(DXform));
+    d.meshes = (const DMesh*)up.put_copy(meshes.data(), meshes.size() * sizeof(DMesh));
+    d.materials = (const hrt_material*)up.put(s.materials.data(), s.materials.size() * sizeof(hrt_material));
+    d.textures = (const DTexture*)up.put_copy(tex.data(), tex.size() * sizeof(DTexture));
+    d.tlas_nodes = (const float4*)up.put(s.tlas.nodes.data(), s.tlas.nodes.size() * sizeof(float4));
+    d.tlas_root = s.tlas.root;
+    d.n_objects = (int)s.d_objects.size();
+    d.n_materials = (int)s.materials.size();
+    d.n_textures = (int)s.textures.size();
+    d.background = s.background;
+    d.fast = fast ? 1 : 0;
+    d.tlas_cull_scale = s.tlas_cull_scale;
+    return d;
+}
+
+} // namespace hrt

@@ -1,0 +1,307 @@
+#!/usr/bin/env python
+"""bench.py — Mrays/s of the path-tracing hot path on N B200s, beside the reference's CPU renderer.
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path (one rank per GPU under torchrun)
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's own CPU renderer on the host cores
+
+A "step" is one full render of the workload (default: BASELINE.json configs[1], shiny_teapot 1920x1080 at 1024 spp)
+with the scene already resident in HBM: raygen -> 50 x (trace, shade + compaction) -> film add, the spp split over the
+ranks, one NCCL reduce of the float film to rank 0, film resolve (mean -> ACES -> sqrt -> 8 bit) on rank 0.
+`value` = rays (closest-hit queries, = world->hit calls of main.cpp:45) of all ranks / max-over-ranks device time.
+`e2e` = the same through the host-buffer C ABI: scene build + commit (host->device upload of geometry, BVHs, textures),
+hrt_render / render_split, device->host read of the float film and the 8-bit image, every step.
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+from hobbyraytracer_b200 import abi, scenes  # noqa: E402
+
+CACHE = os.path.join(ROOT, "tests", "_cache")
+ORACLE_SO = os.path.join(ROOT, "oracle", "_build", "liboracle.so")
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libhrt_ref.so")
+
+
+def make_workload(name, args):
+    """-> (SceneDesc, camera dict, width, height, spp, n_prims-for-B_alg, prim bytes)"""
+    if name == "shiny_teapot":
+        sd, cam, info = scenes.shiny_teapot_scene(CACHE, n=56, env_w=4096, env_h=2048)
+    elif name == "teapot_scene":
+        sd, cam, info = scenes.teapot_scene(CACHE, n=56, env_w=4096, env_h=2048)
+    elif name == "scattered_balls":
+        sd, cam, info = scenes.scattered_balls_scene(seed=42, grid=11)
+    elif name == "cornell_smoke":
+        sd, cam, info = scenes.cornell_smoke_scene()
+    elif name == "big_mesh":
+        sd, cam, info = scenes.big_mesh_scene(CACHE, quads=args.quads)
+    else:
+        raise SystemExit(f"unknown workload {name}")
+    w = args.width or info["width"]; h = args.height or info["height"]; spp = args.spp or info["spp"]
+    return sd, cam, w, h, spp, info
+
+
+def alg_bytes_per_ray(sd):
+    """Algorithmic bytes of one closest-hit query in the traversal kernel: 32 B ray read + 16 B hit
+    written + one root-to-leaf path of 32 B nodes + one primitive (48 B triangle / 16 B sphere / 32 B rect)."""
+    n_prims = 0; prim_bytes = 16
+    for s in sd.shapes:
+        if s[0] == "mesh":
+            n_prims += s[1].shape[0]; prim_bytes = 48
+        elif s[0] == "box":
+            n_prims += 6; prim_bytes = max(prim_bytes, 32)
+        else:
+            n_prims += 1
+            if s[0] == "rect":
+                prim_bytes = max(prim_bytes, 32)
+    depth = int(np.ceil(np.log2(max(n_prims, 2))))
+    return 32 + 16 + 32 * depth + prim_bytes, n_prims
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) >= 6 and r[2 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+
+
+def load_peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    except Exception:
+        return 6650.0, "B200_PROFILING.md fallback 6.65 TB/s (of fallback)"
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def cpu_render_rate(sd, cam, w, h, target_s, seed=1):
+    """The reference's own renderer (oracle/_ref, `reference`) or the oracle restatement (`port`) on all host cores, on a
+    bounded sample of the workload: the full frame at the spp that takes about target_s seconds."""
+    if os.path.exists(REF_SO):
+        lib, kind = abi.Lib(REF_SO, "ref_"), "reference"
+    else:
+        lib, kind = abi.Lib(ORACLE_SO, "orc_"), "port"
+    sc = sd.build(lib, abi.BVH_REFERENCE, 3, tagged=False) if kind == "reference" else sd.build(lib, abi.BVH_REFERENCE, 3)
+    c = scenes.camera_for(cam, w, h)
+    cores = lib.fn("hardware_threads")()
+    # calibrate on a strip of rows: a narrower camera would change the rays, so render whole frames at low spp instead
+    t0 = time.perf_counter(); _, rays1 = sc.render_f32(c, w, h, 1, seed=seed, threads=cores); t1 = time.perf_counter() - t0
+    spp = max(1, min(64, int(target_s / max(t1, 1e-3))))
+    t0 = time.perf_counter(); _, rays = sc.render_f32(c, w, h, spp, seed=seed + 1, threads=cores); dt = time.perf_counter() - t0
+    return {"rays": rays, "seconds": dt, "spp": spp, "cores": cores, "kind": kind, "samples": w * h * spp,
+            "sample": f"full {w}x{h} frame at {spp} spp ({w * h * spp / 1e6:.1f} M camera samples, {rays / 1e6:.1f} M rays, {dt:.1f} s), "
+                      f"{cores} threads, thread-local rand()"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sd, cam, w, h, spp, info = make_workload(args.workload, args)
+    os.makedirs(os.path.join(ROOT, "oracle", "_build"), exist_ok=True)
+    if not os.path.exists(REF_SO) and not os.path.exists(ORACLE_SO):
+        subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "oracle"], check=True)
+    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        r = cpu_render_rate(sd, cam, w, h, per_step / 4)
+    tot_rays = tot_s = tot_samples = 0
+    for _ in range(args.steps):
+        r = cpu_render_rate(sd, cam, w, h, per_step)
+        tot_rays += r["rays"]; tot_s += r["seconds"]; tot_samples += r["samples"]
+    value = tot_rays / tot_s / 1e6
+    line = {"impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * tot_s / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "samples_per_s": tot_samples / tot_s,
+            "config": {"workload": f"{info['name']} {w}x{h}, {info['spp']} spp (CPU arm: bounded sample per step)", "width": w, "height": h, "spp": info["spp"]},
+            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
+            "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def run_own(args):
+    import torch
+    import hobbyraytracer_b200 as pkg
+    from hobbyraytracer_b200 import multigpu
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = pkg.load()
+    lib.check(lib.fn("set_device")(local), "set_device")
+    sd, cam, w, h, spp, info = make_workload(args.workload, args)
+    c = scenes.camera_for(cam, w, h)
+    bvh = abi.BVH_SAH if args.bvh == "sah" else abi.BVH_REFERENCE
+    t0 = time.perf_counter(); sc = sd.build(lib, bvh, 3); t_commit = time.perf_counter() - t0
+    npix = w * h
+    accum = torch.zeros(npix * 3, dtype=torch.float32, device="cuda")
+    rgb8 = torch.zeros(npix * 3, dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    flags = abi.RENDER_MEGAKERNEL if args.megakernel else 0
+
+    def step():
+        accum.zero_()
+        multigpu.render_split(sc, c, w, h, spp, accum, rank, world, dist, seed=args.seed, stream_ptr=stream, rgb8=rgb8, flags=flags)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    sync_all()
+    lib.fn("reset_stats")(sc.h)
+    clocks = ClockSampler(local) if rank == 0 else None
+    if clocks:
+        clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    sync_all()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    st = sc.stats()
+    tot = torch.tensor([float(st.rays), float(st.paths), float(st.launches), float(st.retraced)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX); dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms = float(ms.item()); rays, paths, launches, retraced = [float(x) for x in tot.tolist()]
+    clk = clocks.stop() if clocks else None
+
+    # ---- end to end through the host-buffer C ABI: build + commit (upload) + render + film read-back, every step ----
+    h_sum = torch.empty((h, w, 3), dtype=torch.float32).pin_memory().numpy()
+    h_rgb = torch.empty((h, w, 3), dtype=torch.uint8).pin_memory().numpy()
+
+    def e2e_step():
+        s2 = sd.build(lib, bvh, 3)
+        if world == 1:
+            p = abi.RenderParams(w, h, spp, 0, 0, 50, 0.001, args.seed, 0, flags)
+            import ctypes as C
+            lib.check(lib.fn("render")(s2.h, C.byref(c), C.byref(p), h_sum.ctypes.data, h_rgb.ctypes.data), "render")
+        else:
+            accum.zero_()
+            multigpu.render_split(s2, c, w, h, spp, accum, rank, world, dist, seed=args.seed, stream_ptr=stream, rgb8=rgb8, flags=flags)
+            if rank == 0:
+                torch.from_numpy(h_sum).view(-1).copy_(accum, non_blocking=True)
+                torch.from_numpy(h_rgb).view(-1).copy_(rgb8, non_blocking=True)
+            torch.cuda.synchronize()
+        stt = s2.stats(); s2.close()
+        return stt
+
+    e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    e2e_step(); sync_all()
+    t0 = time.perf_counter(); e2e_rays = 0.0; scene_bytes = 0
+    for _ in range(e2e_steps):
+        stt = e2e_step(); e2e_rays += float(stt.rays); scene_bytes = int(stt.scene_bytes)
+    sync_all()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    e2e_r = torch.tensor([e2e_rays], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX); dist.all_reduce(e2e_r, op=dist.ReduceOp.SUM)
+
+    if rank == 0:
+        peak, peak_src = load_peaks()
+        b_alg, n_prims = alg_bytes_per_ray(sd)
+        rank_rays = float(st.rays)
+        ach = rank_rays * b_alg / (st.ms_trace * 1e-3) / 1e9 if st.ms_trace > 0 else None
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
+        except Exception:
+            pass
+        line = {"metric": "Mrays/s", "value": rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "samples_per_s": paths / (ms * 1e-3), "samples_per_s_per_gpu": paths / (ms * 1e-3) / world, "rays_per_sample": rays / max(paths, 1),
+                "config": {"workload": f"{info['name']} {w}x{h}, {spp} spp split over {world} GPU(s)", "width": w, "height": h, "spp": spp, "max_depth": 50,
+                           "bvh": args.bvh, "n_prims": n_prims, "pipeline": "megakernel" if args.megakernel else "wavefront",
+                           "cache": "working set per wavefront batch (rays+hits+path state of 4 Mi paths = 470 MB) exceeds the 126 MB L2; every batch streams fresh queues"},
+                "e2e": {"value": float(e2e_r.item()) / float(e2e_s.item()) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": scene_bytes,
+                        "d2h_bytes_per_step": npix * 15, "steps": e2e_steps, "includes": "scene build + BVH build + upload, render, float film + 8-bit image read-back"},
+                "gpu_launches": int(launches), "retraced_fraction": retraced / max(rays, 1), "commit_s": t_commit,
+                "kernel_ms": {"trace": st.ms_trace, "shade": st.ms_shade, "other": st.ms_other, "total": st.ms_total, "note": "rank 0, CUDA events inside the timed region"},
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": (ach / peak) if ach else None, "traffic": traffic,
+                             "kernel": "k_trace (+k_trace_retrace)", "alg_bytes_per_ray": b_alg, "peak_source": peak_src,
+                             "note": "latency/divergence-bound pointer chasing; scene fits L2, see DESIGN.md"},
+                "clocks": clk}
+        if world == 1 and not args.no_cpu:
+            try:
+                r = cpu_render_rate(sd, cam, w, h, args.cpu_seconds)
+                line["cpu_baseline"] = {"value": r["rays"] / r["seconds"] / 1e6, "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"],
+                                        "samples_per_s": r["samples"] / r["seconds"]}
+            except Exception as e:  # the checker is missing: say so, never substitute
+                line["cpu_baseline"] = {"value": None, "unit": "Mrays/s", "cores": 0, "kind": "unavailable", "sample": str(e)}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier(); dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--workload", default="shiny_teapot")
+    ap.add_argument("--spp", type=int, default=0, help="samples per pixel per step (default: the workload's own)")
+    ap.add_argument("--width", type=int, default=0); ap.add_argument("--height", type=int, default=0)
+    ap.add_argument("--quads", type=int, default=2290)
+    ap.add_argument("--bvh", default="sah", choices=["sah", "reference"])
+    ap.add_argument("--megakernel", action="store_true")
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_own(args)
+
+
+if __name__ == "__main__":
+    main()

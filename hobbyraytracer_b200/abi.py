@@ -46,7 +46,8 @@ class RenderParams(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("paths", C.c_uint64), ("launches", C.c_uint64), ("ms_trace", C.c_double),
                 ("ms_shade", C.c_double), ("ms_other", C.c_double), ("ms_total", C.c_double),
-                ("node_tests", C.c_uint64), ("prim_tests", C.c_uint64)]
+                ("node_tests", C.c_uint64), ("prim_tests", C.c_uint64), ("retraced", C.c_uint64),
+                ("scene_bytes", C.c_uint64), ("ms_build", C.c_double)]
 
 
 def make_camera(position, look_at, up, vfov_deg, aspect, aperture=0.0, focal_distance=1.0) -> Camera:

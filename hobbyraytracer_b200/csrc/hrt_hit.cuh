@@ -492,12 +492,14 @@ HRT_HDN inline void object_hit_fast(const DScene& s, int i, const Ray& r, float 
     if (hit_object_ref(s, i, r, t_min, cull_bound(b), t, prim, key, bounce)) consider(b, t, t, prim, i);
 }
 
+// Ordered traversal proper.  need_ref is set when the answer depends on the visiting order (see above); the hit
+// returned is then meaningless and the ray must go through trace_ref.
 template <bool COUNT>
-HRT_HDN inline Hit trace_fast(const DScene& s, const Ray& r, float t_min, float t_max, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
+HRT_HDN inline Hit trace_fast_try(const DScene& s, const Ray& r, float t_min, float t_max, const RngKey& key, uint32_t bounce, TraceCounters* cnt, bool& need_ref)
 {
     Best b; b.t = 0.0f; b.a = 0.0f; b.prim = HRT_MISS; b.obj = -1; b.amb = 0; b.bad = 0; b.t_max = t_max;
-    const bool ok = dir_ok(r.d) && hrt_finite(r.o.x) && hrt_finite(r.o.y) && hrt_finite(r.o.z) && s.n_objects > 0;
-    if (ok) {
+    const bool ok = dir_ok(r.d) && hrt_finite(r.o.x) && hrt_finite(r.o.y) && hrt_finite(r.o.z);
+    if (ok && s.n_objects > 0) {
         const V3 id = v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
         // RotateQuat objects report t in units of their normalised direction (rotateQuat.cpp:51):
         // reported t >= world t * |d| * tlas_cull_scale, so entry distances are scaled down before they cull.
@@ -530,11 +532,20 @@ HRT_HDN inline Hit trace_fast(const DScene& s, const Ray& r, float t_min, float 
             node = stack[--sp];
         }
     }
-    if (!ok || b.amb || b.bad) {
+    need_ref = (!ok && s.n_objects > 0) || b.amb || b.bad;
+    Hit h; h.t = b.prim == HRT_MISS ? 0.0f : b.t; h.prim = b.prim; h.obj = b.obj; h.flags = 0;
+    return h;
+}
+
+template <bool COUNT>
+HRT_HDN inline Hit trace_fast(const DScene& s, const Ray& r, float t_min, float t_max, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
+{
+    bool need_ref = false;
+    Hit h = trace_fast_try<COUNT>(s, r, t_min, t_max, key, bounce, cnt, need_ref);
+    if (need_ref) {
         if (COUNT) cnt->fallbacks += 1;
         return trace_ref(s, r, t_min, t_max, key, bounce);
     }
-    Hit h; h.t = b.prim == HRT_MISS ? 0.0f : b.t; h.prim = b.prim; h.obj = b.obj; h.flags = 0;
     return h;
 }
 

@@ -122,6 +122,10 @@ typedef struct hrt_stats {
     double   ms_total;        /* device time of the whole call                                       */
     uint64_t node_tests;      /* only filled by counters-enabled entry points                        */
     uint64_t prim_tests;
+    uint64_t retraced;        /* rays whose answer depended on the visiting order and were re-traced in the
+                                 reference's order (HRT_BVH_SAH only)                                   */
+    uint64_t scene_bytes;     /* bytes of scene data resident in device memory after hrt_scene_commit  */
+    double   ms_build;        /* host time of the BVH builds in hrt_scene_commit                       */
 } hrt_stats;
 
 typedef struct hrt_scene hrt_scene;

@@ -26,7 +26,12 @@ def hsim():
 
 
 def bits(a):
-    return np.ascontiguousarray(a).view(np.uint32)
+    """Bit pattern of fp32 values, with every NaN mapped to one canonical pattern: the sign/payload of a generated NaN is a
+    hardware convention (x86 SSE produces 0xFFC00000, NVIDIA GPUs 0x7FFFFFFF), not arithmetic — NaN *positions* must agree."""
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    b = a.view(np.uint32).copy()
+    b[np.isnan(a)] = 0x7FC00000
+    return b
 
 
 def check_hits(o, h, uv_exact=True, front=True, t_exact=True, skip_uv=None):

@@ -5,8 +5,8 @@
     python bench.py --impl reference --gpus N --steps K ...   # the reference's own CPU renderer on the host cores
 
 A "step" is one full render of the workload (default: BASELINE.json configs[1], shiny_teapot 1920x1080 at 1024 spp)
-with the scene already resident in HBM: raygen -> 50 x (trace, shade + compaction) -> film add, the spp split over the
-ranks, one NCCL reduce of the float film to rank 0, film resolve (mean -> ACES -> sqrt -> 8 bit) on rank 0.
+with the scene already resident in HBM: a persistent wavefront (trace, shade + compaction + path regeneration + film
+add, repeated until the image is out of samples), the spp split over the ranks, one NCCL reduce of the integer film to rank 0, film resolve (mean -> ACES -> sqrt -> 8 bit) on rank 0.
 `value` = rays (closest-hit queries, = world->hit calls of main.cpp:45) of all ranks / max-over-ranks device time.
 `e2e` = the same through the host-buffer C ABI: scene build + commit (host->device upload of geometry, BVHs, textures),
 hrt_render / render_split, device->host read of the float film and the 8-bit image, every step.
@@ -177,14 +177,15 @@ def run_own(args):
     bvh = abi.BVH_SAH if args.bvh == "sah" else abi.BVH_REFERENCE
     t0 = time.perf_counter(); sc = sd.build(lib, bvh, 3); t_commit = time.perf_counter() - t0
     npix = w * h
-    accum = torch.zeros(npix * 3, dtype=torch.float32, device="cuda")
+    film = multigpu.new_film(lib, w, h)
+    fsum = torch.zeros(npix * 3, dtype=torch.float32, device="cuda")
     rgb8 = torch.zeros(npix * 3, dtype=torch.uint8, device="cuda")
     stream = torch.cuda.current_stream().cuda_stream
     flags = abi.RENDER_MEGAKERNEL if args.megakernel else 0
 
     def step():
-        accum.zero_()
-        multigpu.render_split(sc, c, w, h, spp, accum, rank, world, dist, seed=args.seed, stream_ptr=stream, rgb8=rgb8, flags=flags)
+        film.zero_()
+        multigpu.render_split(sc, c, w, h, spp, film, rank, world, dist, seed=args.seed, stream_ptr=stream, rgb8=rgb8, flags=flags)
 
     def sync_all():
         torch.cuda.synchronize()
@@ -207,10 +208,10 @@ def run_own(args):
     sync_all()
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
     st = sc.stats()
-    tot = torch.tensor([float(st.rays), float(st.paths), float(st.launches), float(st.retraced)], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([float(st.rays), float(st.paths), float(st.launches)], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX); dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    ms = float(ms.item()); rays, paths, launches, retraced = [float(x) for x in tot.tolist()]
+    ms = float(ms.item()); rays, paths, launches = [float(x) for x in tot.tolist()]
     clk = clocks.stop() if clocks else None
 
     # ---- end to end through the host-buffer C ABI: build + commit (upload) + render + film read-back, every step ----
@@ -224,10 +225,10 @@ def run_own(args):
             import ctypes as C
             lib.check(lib.fn("render")(s2.h, C.byref(c), C.byref(p), h_sum.ctypes.data, h_rgb.ctypes.data), "render")
         else:
-            accum.zero_()
-            multigpu.render_split(s2, c, w, h, spp, accum, rank, world, dist, seed=args.seed, stream_ptr=stream, rgb8=rgb8, flags=flags)
+            film.zero_()
+            multigpu.render_split(s2, c, w, h, spp, film, rank, world, dist, seed=args.seed, stream_ptr=stream, rgb8=rgb8, total=fsum, flags=flags)
             if rank == 0:
-                torch.from_numpy(h_sum).view(-1).copy_(accum, non_blocking=True)
+                torch.from_numpy(h_sum).view(-1).copy_(fsum, non_blocking=True)
                 torch.from_numpy(h_rgb).view(-1).copy_(rgb8, non_blocking=True)
             torch.cuda.synchronize()
         stt = s2.stats(); s2.close()
@@ -258,14 +259,14 @@ def run_own(args):
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "samples_per_s": paths / (ms * 1e-3), "samples_per_s_per_gpu": paths / (ms * 1e-3) / world, "rays_per_sample": rays / max(paths, 1),
                 "config": {"workload": f"{info['name']} {w}x{h}, {spp} spp split over {world} GPU(s)", "width": w, "height": h, "spp": spp, "max_depth": 50,
-                           "bvh": args.bvh, "n_prims": n_prims, "pipeline": "megakernel" if args.megakernel else "wavefront",
-                           "cache": "working set per wavefront batch (rays+hits+path state of 4 Mi paths = 470 MB) exceeds the 126 MB L2; every batch streams fresh queues"},
+                           "bvh": args.bvh, "n_prims": n_prims, "pipeline": "megakernel" if args.megakernel else "persistent wavefront",
+                           "cache": "the wavefront queues (4 Mi entries: rays + hits + path state = 600 MB) exceed the 126 MB L2 and are rewritten every pass; no flush needed"},
                 "e2e": {"value": float(e2e_r.item()) / float(e2e_s.item()) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": scene_bytes,
                         "d2h_bytes_per_step": npix * 15, "steps": e2e_steps, "includes": "scene build + BVH build + upload, render, float film + 8-bit image read-back"},
-                "gpu_launches": int(launches), "retraced_fraction": retraced / max(rays, 1), "commit_s": t_commit,
+                "gpu_launches": int(launches), "commit_s": t_commit,
                 "kernel_ms": {"trace": st.ms_trace, "shade": st.ms_shade, "other": st.ms_other, "total": st.ms_total, "note": "rank 0, CUDA events inside the timed region"},
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": (ach / peak) if ach else None, "traffic": traffic,
-                             "kernel": "k_trace (+k_trace_retrace)", "alg_bytes_per_ray": b_alg, "peak_source": peak_src,
+                             "kernel": "k_wave_trace", "alg_bytes_per_ray": b_alg, "peak_source": peak_src,
                              "note": "latency/divergence-bound pointer chasing; scene fits L2, see DESIGN.md"},
                 "clocks": clk}
         if world == 1 and not args.no_cpu:

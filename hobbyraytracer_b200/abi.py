@@ -123,7 +123,8 @@ class Lib:
         self._sig("set_device", i, [i], required=False)
         self._sig("render", i, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp], required=False)
         self._sig("render_accumulate_device", i, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp], required=False)
-        self._sig("film_resolve_device", i, [_vp, _vp, i, i, i, _vp, _vp, _vp], required=False)
+        self._sig("film_resolve_device", i, [_vp, _vp, i, i, i, _vp, _vp, _vp, _vp], required=False)
+        self._sig("film_bytes", i, [i, i], required=False)
         self._sig("get_stats", i, [_vp, C.POINTER(Stats)], required=False)
         self._sig("reset_stats", i, [_vp], required=False)
         # oracle-only

@@ -10,7 +10,7 @@
 #include <string>
 #include <vector>
 
-#include "hrt_hit.cuh"
+#include "hrt_trace.cuh"
 #include "hrt_kernels.h"
 #include "hrt_upload.h"
 
@@ -53,29 +53,33 @@ struct hrt_scene {
     cudaStream_t stream = nullptr;
     std::vector<void*> scene_allocs;
     size_t scene_bytes = 0;
-    // wavefront working set
-    RenderJob job{};
-    long long job_capacity = 0; int job_depth = 0;
-    float* d_accum = nullptr; size_t accum_elems = 0;
-    std::vector<cudaEvent_t> events;            // 2 pools x (2 trace + 1 shade + 2 batch) per bounce
+    // persistent-wavefront working set
+    WaveJob job{};
+    unsigned int job_capacity = 0;
+    long long* d_film = nullptr; size_t film_pixels = 0;       // film of hrt_render() + 8-bit image + float sums behind it
+    float* d_out = nullptr; size_t out_pixels = 0;
+    WaveCtl* h_ctl = nullptr;                                   // pinned snapshots of the control block (ring of CTL_RING)
+    std::vector<cudaEvent_t> events;
     // ray-batch working set
-    float4* tb_rays = nullptr; Hit* tb_hits = nullptr; unsigned int* tb_retrace = nullptr; unsigned int* tb_n_retrace = nullptr;
+    float4* tb_rays = nullptr; Hit* tb_hits = nullptr;
     uint32_t* tb_prim = nullptr; float* tb_t = nullptr; long long tb_capacity = 0;
     hrt_stats stats{};
 };
 
 namespace {
 
+constexpr int CTL_RING = 4;
+
 void free_job(hrt_scene* s)
 {
-    cudaFree(s->job.rays[0]); cudaFree(s->job.rays[1]); cudaFree(s->job.hits); cudaFree(s->job.atten); cudaFree(s->job.radiance);
-    cudaFree(s->job.counts); cudaFree(s->job.retrace); cudaFree(s->job.n_retrace); cudaFree(s->job.totals);
-    s->job = RenderJob{}; s->job_capacity = 0; s->job_depth = 0;
+    for (int q = 0; q < 2; ++q) { cudaFree(s->job.rays[q]); cudaFree(s->job.thr[q]); cudaFree(s->job.res[q]); }
+    cudaFree(s->job.hits); cudaFree(s->job.ctl);
+    s->job = WaveJob{}; s->job_capacity = 0;
 }
 void free_tb(hrt_scene* s)
 {
-    cudaFree(s->tb_rays); cudaFree(s->tb_hits); cudaFree(s->tb_retrace); cudaFree(s->tb_n_retrace); cudaFree(s->tb_prim); cudaFree(s->tb_t);
-    s->tb_rays = nullptr; s->tb_hits = nullptr; s->tb_retrace = nullptr; s->tb_n_retrace = nullptr; s->tb_prim = nullptr; s->tb_t = nullptr; s->tb_capacity = 0;
+    cudaFree(s->tb_rays); cudaFree(s->tb_hits); cudaFree(s->tb_prim); cudaFree(s->tb_t);
+    s->tb_rays = nullptr; s->tb_hits = nullptr; s->tb_prim = nullptr; s->tb_t = nullptr; s->tb_capacity = 0;
 }
 void free_scene_device(hrt_scene* s)
 {
@@ -83,20 +87,19 @@ void free_scene_device(hrt_scene* s)
     s->scene_allocs.clear(); s->scene_bytes = 0;
 }
 
-int ensure_job(hrt_scene* s, long long capacity, int max_depth)
+int ensure_job(hrt_scene* s, unsigned int capacity)
 {
-    if (capacity <= s->job_capacity && max_depth <= s->job_depth) return 0;
+    if (capacity <= s->job_capacity) return 0;
     free_job(s);
-    CK(cudaMalloc(&s->job.rays[0], sizeof(float4) * 2 * (size_t)capacity));
-    CK(cudaMalloc(&s->job.rays[1], sizeof(float4) * 2 * (size_t)capacity));
+    for (int q = 0; q < 2; ++q) {
+        CK(cudaMalloc(&s->job.rays[q], sizeof(float4) * 2 * (size_t)capacity));
+        CK(cudaMalloc(&s->job.thr[q], sizeof(float4) * (size_t)capacity));
+        CK(cudaMalloc(&s->job.res[q], sizeof(float4) * (size_t)capacity));
+    }
     CK(cudaMalloc(&s->job.hits, sizeof(Hit) * (size_t)capacity));
-    CK(cudaMalloc(&s->job.atten, sizeof(float4) * (size_t)capacity));
-    CK(cudaMalloc(&s->job.radiance, sizeof(float4) * (size_t)capacity));
-    CK(cudaMalloc(&s->job.counts, sizeof(unsigned int) * (size_t)(max_depth + 1)));
-    CK(cudaMalloc(&s->job.retrace, sizeof(unsigned int) * (size_t)capacity));
-    CK(cudaMalloc(&s->job.n_retrace, sizeof(unsigned int) * (size_t)(max_depth + 1)));
-    CK(cudaMalloc(&s->job.totals, sizeof(unsigned long long) * 2));
-    s->job_capacity = capacity; s->job_depth = max_depth;
+    CK(cudaMalloc(&s->job.ctl, sizeof(WaveCtl)));
+    if (!s->h_ctl) CK(cudaMallocHost(&s->h_ctl, sizeof(WaveCtl) * CTL_RING));
+    s->job_capacity = capacity;
     return 0;
 }
 int ensure_tb(hrt_scene* s, long long n, bool own_rays)
@@ -105,8 +108,6 @@ int ensure_tb(hrt_scene* s, long long n, bool own_rays)
         free_tb(s);
         CK(cudaMalloc(&s->tb_rays, sizeof(float4) * 2 * (size_t)n));
         CK(cudaMalloc(&s->tb_hits, sizeof(Hit) * (size_t)n));
-        CK(cudaMalloc(&s->tb_retrace, sizeof(unsigned int) * (size_t)n));
-        CK(cudaMalloc(&s->tb_n_retrace, sizeof(unsigned int)));
         CK(cudaMalloc(&s->tb_prim, sizeof(uint32_t) * (size_t)n));
         CK(cudaMalloc(&s->tb_t, sizeof(float) * (size_t)n));
         s->tb_capacity = n;
@@ -115,11 +116,13 @@ int ensure_tb(hrt_scene* s, long long n, bool own_rays)
     return 0;
 }
 
-long long batch_paths()
+unsigned int wave_capacity()
 {
-    const char* e = getenv("HRT_BATCH_PATHS");
+    const char* e = getenv("HRT_WAVE_CAPACITY");
     long long v = e ? atoll(e) : 0;
-    return v > 0 ? v : (4ll << 20);
+    if (v < 1024) v = 4ll << 20;
+    if (v > (1ll << 30)) v = 1ll << 30;
+    return (unsigned int)v;
 }
 
 int check_render_args(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p)
@@ -132,53 +135,80 @@ int check_render_args(hrt_scene* s, const hrt_camera* cam, const hrt_render_para
     return 0;
 }
 
-// renders samples [first, first+count) of every pixel and adds them into d_accum (sum, not mean)
-int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, float* d_accum, cudaStream_t st)
+// renders samples [first, first+count) of every pixel and adds them into the fixed-point film d_film
+int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, long long* d_film, cudaStream_t st)
 {
     const int npix = p->width * p->height;
     const int first = p->sample_first, count = p->sample_count > 0 ? p->sample_count : p->spp;
     const int max_depth = p->max_depth > 0 ? p->max_depth : 50;
     const bool mega = (p->flags & HRT_RENDER_MEGAKERNEL) != 0;
-    long long per_batch = batch_paths() / npix; if (per_batch < 1) per_batch = 1; if (per_batch > count) per_batch = count;
-    int rc = ensure_job(s, (long long)npix * per_batch, max_depth); if (rc < 0) return rc;
-    RenderJob j = s->job;
+    const unsigned long long total = (unsigned long long)npix * (unsigned long long)count;
+    unsigned long long cap = wave_capacity();
+    if (cap > total) cap = (total + 1023ull) / 1024ull * 1024ull;
+    if (mega) cap = 1024;
+    int rc = ensure_job(s, (unsigned int)cap); if (rc < 0) return rc;
+    WaveJob j = s->job;
     j.width = p->width; j.height = p->height; j.npix = npix; j.max_depth = max_depth;
+    const bool tiled = (p->width % 8 == 0) && (p->height % 4 == 0);
+    j.tiles_x = tiled ? p->width / 8 : 0; j.tiles_y = tiled ? p->height / 4 : 0;
     j.t_min = p->t_min > 0 ? p->t_min : 0.001f; j.seed = p->seed; j.rng_mode = p->rng_mode;
-    DCamera dc = make_camera(*cam);
-    CK(cudaMemsetAsync(j.totals, 0, sizeof(unsigned long long) * 2, st));
-    // events: per pool 3 per bounce + 2 for the whole batch
-    const size_t per_pool = (size_t)max_depth * 3 + 2;
-    while (s->events.size() < per_pool * 2) { cudaEvent_t e; CK(cudaEventCreate(&e)); s->events.push_back(e); }
-    auto collect = [&](int pool) -> int {
-        cudaEvent_t* ev = s->events.data() + per_pool * (size_t)pool;
-        CK(cudaEventSynchronize(ev[per_pool - 1]));
-        float ms = 0;
-        if (!mega)
-            for (int b = 0; b < max_depth; ++b) {
-                CK(cudaEventElapsedTime(&ms, ev[2 * b], ev[2 * b + 1])); s->stats.ms_trace += ms;
-                CK(cudaEventElapsedTime(&ms, ev[2 * b + 1], ev[2 * max_depth + b])); s->stats.ms_shade += ms;
+    j.s_first = first; j.s_count = count; j.capacity = (unsigned int)cap; j.film = d_film;
+    const DCamera dc = make_camera(*cam);
+
+    constexpr int CHUNK = 8;                              // iterations between two looks at the control block
+    constexpr int EV_PER_CHUNK = 2 * CHUNK + 2;           // per iteration: before trace, before shade; + chunk end + snapshot
+    while (s->events.size() < (size_t)(EV_PER_CHUNK * CTL_RING + 2)) { cudaEvent_t e; CK(cudaEventCreate(&e)); s->events.push_back(e); }
+    cudaEvent_t ev_begin = s->events[EV_PER_CHUNK * CTL_RING], ev_end = s->events[EV_PER_CHUNK * CTL_RING + 1];
+
+    WaveCtl init{}; init.total_paths = total;
+    CK(cudaMemcpyAsync(j.ctl, &init, sizeof(init), cudaMemcpyHostToDevice, st));
+    CK(cudaEventRecord(ev_begin, st));
+    s->stats.paths += total;
+    if (mega) {
+        launch_render_mega(s->d, j, dc, s->sm_count, st, &s->stats.launches);
+    } else {
+        launch_wave_init(j, dc, s->sm_count, st, &s->stats.launches);
+        int it = 0, issued = 0, retired = 0; bool done = false;
+        auto retire = [&](int chunk) -> int {               // waits for the chunk, adds its kernel times, looks at its snapshot
+            cudaEvent_t* ev = s->events.data() + (size_t)EV_PER_CHUNK * (size_t)(chunk % CTL_RING);
+            CK(cudaEventSynchronize(ev[2 * CHUNK + 1]));
+            float ms = 0;
+            for (int k = 0; k < CHUNK; ++k) {
+                CK(cudaEventElapsedTime(&ms, ev[2 * k], ev[2 * k + 1])); s->stats.ms_trace += ms;
+                CK(cudaEventElapsedTime(&ms, ev[2 * k + 1], ev[2 * k + 2])); s->stats.ms_shade += ms;
             }
-        CK(cudaEventElapsedTime(&ms, ev[per_pool - 2], ev[per_pool - 1])); s->stats.ms_total += ms;
-        return 0;
-    };
-    int batch = 0;
-    for (int done = 0; done < count; ++batch) {
-        int n = (int)std::min<long long>(per_batch, count - done);
-        int pool = batch & 1;
-        if (batch >= 2) { rc = collect(pool); if (rc < 0) return rc; }
-        cudaEvent_t* ev = s->events.data() + per_pool * (size_t)pool;
-        CK(cudaEventRecord(ev[per_pool - 2], st));
-        launch_render_batch(s->d, j, dc, first + done, n, d_accum, mega, s->sm_count, st, &s->stats.launches, mega ? nullptr : ev, mega ? nullptr : ev + 2 * max_depth);
-        CK(cudaEventRecord(ev[per_pool - 1], st));
-        CK(cudaGetLastError());
-        done += n;
-        s->stats.paths += (uint64_t)npix * (uint64_t)n;
+            const WaveCtl& c = s->h_ctl[chunk % CTL_RING];
+            const int o = (chunk * CHUNK + CHUNK) & 1;       // queue the last shade pass of the chunk filled
+            const unsigned long long handed = c.next_path < c.total_paths ? c.next_path : c.total_paths;
+            if (c.n_front[o] == 0 && handed == c.base[o] && handed == c.total_paths) done = true;
+            return 0;
+        };
+        while (!done) {
+            if (issued - retired >= CTL_RING - 1) { rc = retire(retired++); if (rc < 0) return rc; if (done) break; }
+            cudaEvent_t* ev = s->events.data() + (size_t)EV_PER_CHUNK * (size_t)(issued % CTL_RING);
+            for (int k = 0; k < CHUNK; ++k, ++it) {
+                CK(cudaEventRecord(ev[2 * k], st));
+                launch_wave_trace(s->d, j, it, s->sm_count, st, &s->stats.launches);
+                CK(cudaEventRecord(ev[2 * k + 1], st));
+                launch_wave_shade(s->d, j, dc, it, s->sm_count, st, &s->stats.launches);
+            }
+            CK(cudaEventRecord(ev[2 * CHUNK], st));
+            CK(cudaMemcpyAsync(&s->h_ctl[issued % CTL_RING], j.ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, st));
+            CK(cudaEventRecord(ev[2 * CHUNK + 1], st));
+            CK(cudaGetLastError());
+            ++issued;
+        }
+        while (retired < issued) { rc = retire(retired++); if (rc < 0) return rc; }
     }
-    for (int k = std::max(0, batch - 2); k < batch; ++k) { rc = collect(k & 1); if (rc < 0) return rc; }
-    unsigned long long totals[2] = {0, 0};
-    CK(cudaMemcpyAsync(totals, j.totals, sizeof(totals), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(ev_end, st));
+    WaveCtl fin{};
+    CK(cudaMemcpyAsync(&s->h_ctl[0], j.ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    s->stats.rays += totals[0]; s->stats.retraced += totals[1];
+    CK(cudaGetLastError());
+    fin = s->h_ctl[0];
+    float ms = 0; CK(cudaEventElapsedTime(&ms, ev_begin, ev_end));
+    s->stats.ms_total += ms;
+    s->stats.rays += fin.rays;
     s->stats.ms_other = s->stats.ms_total - s->stats.ms_trace - s->stats.ms_shade;
     return 0;
 }
@@ -214,7 +244,8 @@ void hrt_scene_destroy(hrt_scene* s)
     if (s->host.committed || s->stream) {
         cudaSetDevice(s->device);
         free_job(s); free_tb(s); free_scene_device(s);
-        cudaFree(s->d_accum);
+        cudaFree(s->d_film); cudaFree(s->d_out);
+        if (s->h_ctl) cudaFreeHost(s->h_ctl);
         for (cudaEvent_t e : s->events) cudaEventDestroy(e);
         if (s->stream) cudaStreamDestroy(s->stream);
     }
@@ -272,7 +303,7 @@ int hrt_trace_batch_device(hrt_scene* s, const void* d_rays, int64_t n, void* d_
     if (n > s->tb_capacity) {                      // only hits / retrace list are needed for a device call; allocate the full set for simplicity
         int rc = ensure_tb(s, n, false); if (rc < 0) return rc;
     }
-    launch_trace_batch(s->d, (const float4*)d_rays, n, s->tb_hits, rng_seed, s->tb_retrace, s->tb_n_retrace, s->sm_count, st, &s->stats.launches);
+    launch_trace_batch(s->d, (const float4*)d_rays, n, s->tb_hits, rng_seed, s->sm_count, st, &s->stats.launches);
     launch_split_hits(s->tb_hits, n, (uint32_t*)d_prim_id, (float*)d_t, s->sm_count, st, &s->stats.launches);
     CK(cudaGetLastError());
     s->stats.rays += (uint64_t)n;
@@ -308,20 +339,26 @@ int hrt_trace_batch(hrt_scene* s, const float* rays, int64_t n, uint32_t* prim_i
     return 0;
 }
 
-int hrt_render_accumulate_device(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, void* d_accum, void* stream)
+int hrt_film_bytes(int width, int height)
 {
-    int rc = check_render_args(s, cam, p); if (rc < 0) return rc;
-    if (!d_accum) { g_err = "d_accum is NULL"; return HRT_ERR_ARG; }
-    CK(cudaSetDevice(s->device));
-    return render_into(s, cam, p, (float*)d_accum, stream ? (cudaStream_t)stream : s->stream);
+    if (width < 1 || height < 1 || (long long)width * height > 0x3fffffffll / 8) { g_err = "bad film size"; return HRT_ERR_ARG; }
+    return (int)((long long)width * height * FILM_LANES * (long long)sizeof(long long));
 }
 
-int hrt_film_resolve_device(hrt_scene* s, const void* d_accum, int width, int height, int spp, void* d_mean, void* d_rgb8, void* stream)
+int hrt_render_accumulate_device(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, void* d_film, void* stream)
 {
-    if (!s || !d_accum || width < 1 || height < 1 || spp < 1) { g_err = "bad argument"; return HRT_ERR_ARG; }
+    int rc = check_render_args(s, cam, p); if (rc < 0) return rc;
+    if (!d_film) { g_err = "d_film is NULL"; return HRT_ERR_ARG; }
+    CK(cudaSetDevice(s->device));
+    return render_into(s, cam, p, (long long*)d_film, stream ? (cudaStream_t)stream : s->stream);
+}
+
+int hrt_film_resolve_device(hrt_scene* s, const void* d_film, int width, int height, int spp, void* d_sum, void* d_mean, void* d_rgb8, void* stream)
+{
+    if (!s || !d_film || width < 1 || height < 1 || spp < 1) { g_err = "bad argument"; return HRT_ERR_ARG; }
     CK(cudaSetDevice(s->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
-    launch_film_resolve((const float*)d_accum, width * height, spp, (float*)d_mean, (uint8_t*)d_rgb8, s->sm_count, st, &s->stats.launches);
+    launch_film_resolve((const long long*)d_film, width * height, spp, (float*)d_sum, (float*)d_mean, (uint8_t*)d_rgb8, s->sm_count, st, &s->stats.launches);
     CK(cudaGetLastError());
     return 0;
 }
@@ -331,20 +368,20 @@ int hrt_render(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, 
     int rc = check_render_args(s, cam, p); if (rc < 0) return rc;
     CK(cudaSetDevice(s->device));
     const size_t npix = (size_t)p->width * p->height;
-    if (s->accum_elems < npix * 3) {
-        cudaFree(s->d_accum); s->d_accum = nullptr; s->accum_elems = 0;
-        CK(cudaMalloc(&s->d_accum, sizeof(float) * npix * 3 + npix * 3));
-        s->accum_elems = npix * 3;
+    if (s->film_pixels < npix) {
+        cudaFree(s->d_film); s->d_film = nullptr; s->film_pixels = 0;
+        cudaFree(s->d_out); s->d_out = nullptr;
+        CK(cudaMalloc(&s->d_film, sizeof(long long) * FILM_LANES * npix));
+        CK(cudaMalloc(&s->d_out, sizeof(float) * npix * 3 + npix * 3));
+        s->film_pixels = npix;
     }
     cudaStream_t st = s->stream;
-    CK(cudaMemsetAsync(s->d_accum, 0, sizeof(float) * npix * 3, st));
-    rc = render_into(s, cam, p, s->d_accum, st); if (rc < 0) return rc;
-    if (out_sum) CK(cudaMemcpyAsync(out_sum, s->d_accum, sizeof(float) * npix * 3, cudaMemcpyDeviceToHost, st));
-    if (out_rgb8) {
-        uint8_t* d_rgb8 = (uint8_t*)(s->d_accum + npix * 3);
-        launch_film_resolve(s->d_accum, (int)npix, p->spp, nullptr, d_rgb8, s->sm_count, st, &s->stats.launches);
-        CK(cudaMemcpyAsync(out_rgb8, d_rgb8, npix * 3, cudaMemcpyDeviceToHost, st));
-    }
+    CK(cudaMemsetAsync(s->d_film, 0, sizeof(long long) * FILM_LANES * npix, st));
+    rc = render_into(s, cam, p, s->d_film, st); if (rc < 0) return rc;
+    uint8_t* d_rgb8 = (uint8_t*)(s->d_out + npix * 3);
+    launch_film_resolve(s->d_film, (int)npix, p->spp, out_sum ? s->d_out : nullptr, nullptr, out_rgb8 ? d_rgb8 : nullptr, s->sm_count, st, &s->stats.launches);
+    if (out_sum) CK(cudaMemcpyAsync(out_sum, s->d_out, sizeof(float) * npix * 3, cudaMemcpyDeviceToHost, st));
+    if (out_rgb8) CK(cudaMemcpyAsync(out_rgb8, d_rgb8, npix * 3, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
     return 0;

@@ -21,11 +21,6 @@ namespace hrt {
 #define HRT_LD4(p) (*(p))
 #endif
 
-constexpr float NEAR_EPS = 1e-5f;            // relative distance under which two candidate hits count as a tie
-constexpr float CULL_MARGIN = 0.0625f;       // ordered traversal keeps everything that starts within 6.25 % beyond the best candidate
-constexpr float SHEAR_LIMIT = 64.0f;         // max|d| / |d[kZ]| above which ITriangle's t is too inaccurate to order by (see trace_fast)
-constexpr float SLAB_WIDEN = 4.76837158e-7f; // 2^-21: widening of the SAH-node slab interval (conservative vs aabb.h)
-
 struct Hit {                                 // 16-byte hit record written by the traversal kernel
     float t;
     uint32_t prim;                           // HRT_MISS on a miss
@@ -373,178 +368,6 @@ HRT_HDN inline Hit trace_ref(const DScene& s, const Ray& r, float t_min, float t
     if (h.obj >= 0 && stale.obj >= 0 && is_bare_mesh(s.objects[h.obj])) {
         Rec tmp; eval_hit(s, r, stale, tmp);
         h.flags = tmp.front ? 1 : 0;
-    }
-    return h;
-}
-
-// ---- ordered traversal ------------------------------------------------------------------------------------------------
-// Why an ordered traversal can reproduce a sequential one.  The reference accepts primitive i when it is visited
-// with closest >= a_i, and then sets closest = t_i.  For spheres, rects and media a_i = t_i.  A triangle is only
-// reached through its bottom BVH node, whose slab test needs closest > entry, so a_i = max(entry_i, t_i); ITriangle's
-// t can be badly conditioned (its shear axis comes from the ray origin, triangle.cpp:70), so entry_i > t_i happens.
-// If the candidate m with the smallest t has a_m below every other candidate's t, every visiting order ends with m.
-// Anything else — (near-)ties, a_m reaching past another candidate, NaN t, zero direction components, a shear so
-// large that a triangle culled here might report a t far in front of its own box — is re-traced with trace_ref.
-struct Best { float t, a; uint32_t prim; int obj; int amb; int bad; float t_max; };
-
-HRT_HD float cull_bound(const Best& b)      // nothing that starts beyond this can take part in the decision
-{ return b.prim == HRT_MISS ? b.t_max : b.a + CULL_MARGIN * fabsf(b.a); }
-
-HRT_HD void consider(Best& b, float t, float a, uint32_t prim, int obj)
-{
-    if (t != t || a != a) { b.bad = 1; return; }                                // NaN t poisons `closest` in the reference
-    if (b.prim == HRT_MISS) { b.t = t; b.a = a; b.prim = prim; b.obj = obj; return; }
-    if (t < b.t) {
-        b.amb = (a + 2.0f * NEAR_EPS * fabsf(a) >= b.t) ? 1 : 0;                // clear of the old best (and of its ties)?
-        b.t = t; b.a = a; b.prim = prim; b.obj = obj;
-    } else if (t <= b.a + NEAR_EPS * fabsf(b.a)) b.amb = 1;
-}
-
-// Slab test of the two children stored in an SAH node against (o, 1/d); conservative with respect to aabb.h's
-// divisions (one extra rounding from the reciprocal, covered by SLAB_WIDEN).
-HRT_HD void slab2(const float4& n0, const float4& n1, const float4& n2, V3 o, V3 id, float& tn0, float& tf0, float& tn1, float& tf1)
-{
-    float ax = (n0.x - o.x) * id.x, bx = (n0.y - o.x) * id.x, ay = (n0.z - o.y) * id.y, by = (n0.w - o.y) * id.y;
-    float az = (n2.x - o.z) * id.z, bz = (n2.y - o.z) * id.z;
-    tn0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
-    tf0 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
-    float cx = (n1.x - o.x) * id.x, dx = (n1.y - o.x) * id.x, cy = (n1.z - o.y) * id.y, dy = (n1.w - o.y) * id.y;
-    float cz = (n2.z - o.z) * id.z, dz = (n2.w - o.z) * id.z;
-    tn1 = fmaxf(fmaxf(fminf(cx, dx), fminf(cy, dy)), fminf(cz, dz));
-    tf1 = fminf(fminf(fmaxf(cx, dx), fmaxf(cy, dy)), fmaxf(cz, dz));
-    tn0 -= fabsf(tn0) * SLAB_WIDEN; tf0 += fabsf(tf0) * SLAB_WIDEN;
-    tn1 -= fabsf(tn1) * SLAB_WIDEN; tf1 += fabsf(tf1) * SLAB_WIDEN;
-}
-
-HRT_HD bool dir_ok(V3 d)                    // every component non-zero with a finite reciprocal
-{
-    return hrt_finite(1.0f / d.x) && hrt_finite(1.0f / d.y) && hrt_finite(1.0f / d.z);
-}
-
-struct TraceCounters { unsigned long long nodes, prims, fallbacks; };
-
-// per-mesh SAH tree over the reference's bottom nodes
-template <bool COUNT>
-HRT_HDN inline void mesh_hit_fast(const DMesh& m, const Ray& lr, float t_min, Best& b, int obj, TraceCounters* cnt)
-{
-    if (m.ref_root < 0) return;
-    const V3 id = v3(1.0f / lr.d.x, 1.0f / lr.d.y, 1.0f / lr.d.z);
-    const float t_lo = fminf(t_min, 0.0f);           // ITriangle::hit ignores t_min but only reports t > 0
-    int stack[FAST_MAX_DEPTH + 4]; int sp = 0;
-    int node = m.fast_root;
-    for (;;) {
-        if (node >= 0) {
-            const float4* N = m.fast_nodes + 4 * (size_t)node;
-            float4 n0 = HRT_LD4(N), n1 = HRT_LD4(N + 1), n2 = HRT_LD4(N + 2), n3 = HRT_LD4(N + 3);
-            float tn0, tf0, tn1, tf1;
-            slab2(n0, n1, n2, lr.o, id, tn0, tf0, tn1, tf1);
-            if (COUNT) cnt->nodes += 2;
-            const float bound = cull_bound(b);
-            bool h0 = tn0 <= tf0 && tf0 >= t_lo && tn0 <= bound;
-            bool h1 = tn1 <= tf1 && tf1 >= t_lo && tn1 <= bound;
-            int c0 = float_as_int(n3.x), c1 = float_as_int(n3.y);
-            if (h0 && h1) {
-                if (tn1 < tn0) { int tmp = c0; c0 = c1; c1 = tmp; }
-                stack[sp++] = c1; node = c0; continue;
-            }
-            if (h0) { node = c0; continue; }
-            if (h1) { node = c1; continue; }
-        } else {
-            const float4* L = m.fast_leaves + 8 * (size_t)(~node);
-            float4 a = HRT_LD4(L), c = HRT_LD4(L + 1);
-            if (COUNT) cnt->nodes += 1;
-            float entry;
-            if (hit_aabb_entry(xyz(a), xyz(c), lr, t_min, cull_bound(b), entry)) {   // the reference's bottom node box, its arithmetic
-                int triL = float_as_int(a.w), triR = float_as_int(c.w);
-                float tt, b0, b1, b2;
-                float4 p0 = HRT_LD4(L + 2), p1 = HRT_LD4(L + 3), p2 = HRT_LD4(L + 4);
-                if (COUNT) cnt->prims += 1;
-                if (itriangle(xyz(p0), xyz(p1), xyz(p2), lr, cull_bound(b), tt, b0, b1, b2)) consider(b, tt, fmaxf(entry, tt), m.prim_base + (uint32_t)triL, obj);
-                if (triR != triL) {
-                    p0 = HRT_LD4(L + 5); p1 = HRT_LD4(L + 6); p2 = HRT_LD4(L + 7);
-                    if (COUNT) cnt->prims += 1;
-                    if (itriangle(xyz(p0), xyz(p1), xyz(p2), lr, cull_bound(b), tt, b0, b1, b2)) consider(b, tt, fmaxf(entry, tt), m.prim_base + (uint32_t)triR, obj);
-                }
-            }
-        }
-        if (sp == 0) break;
-        node = stack[--sp];
-    }
-}
-
-template <bool COUNT>
-HRT_HDN inline void object_hit_fast(const DScene& s, int i, const Ray& r, float t_min, Best& b, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
-{
-    const DObject& ob = s.objects[i];
-    if (ob.kind == SHAPE_MESH && !ob.medium) {
-        Ray lr = to_local(s, ob, r);
-        if (!dir_ok(lr.d) || !(hrt_finite(lr.o.x) && hrt_finite(lr.o.y) && hrt_finite(lr.o.z))) { b.bad = 1; return; }
-        {   // conditioning of ITriangle's shear for this ray: its kZ is picked from the ORIGIN (triangle.cpp:70)
-            int kZ = lr.o.x > lr.o.z ? (lr.o.x > lr.o.y ? 0 : 1) : 2;
-            float dmax = fmaxf(fmaxf(fabsf(lr.d.x), fabsf(lr.d.y)), fabsf(lr.d.z));
-            if (!(dmax <= SHEAR_LIMIT * fabsf(comp(lr.d, kZ)))) { b.bad = 1; return; }
-        }
-        mesh_hit_fast<COUNT>(s.meshes[ob.mesh], lr, t_min, b, i, cnt);
-        return;
-    }
-    float t; uint32_t prim;
-    if (COUNT) cnt->prims += 1;
-    if (hit_object_ref(s, i, r, t_min, cull_bound(b), t, prim, key, bounce)) consider(b, t, t, prim, i);
-}
-
-// Ordered traversal proper.  need_ref is set when the answer depends on the visiting order (see above); the hit
-// returned is then meaningless and the ray must go through trace_ref.
-template <bool COUNT>
-HRT_HDN inline Hit trace_fast_try(const DScene& s, const Ray& r, float t_min, float t_max, const RngKey& key, uint32_t bounce, TraceCounters* cnt, bool& need_ref)
-{
-    Best b; b.t = 0.0f; b.a = 0.0f; b.prim = HRT_MISS; b.obj = -1; b.amb = 0; b.bad = 0; b.t_max = t_max;
-    const bool ok = dir_ok(r.d) && hrt_finite(r.o.x) && hrt_finite(r.o.y) && hrt_finite(r.o.z);
-    if (ok && s.n_objects > 0) {
-        const V3 id = v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
-        // RotateQuat objects report t in units of their normalised direction (rotateQuat.cpp:51):
-        // reported t >= world t * |d| * tlas_cull_scale, so entry distances are scaled down before they cull.
-        const float cull = s.tlas_cull_scale > 0.0f ? fminf(1.0f, length(r.d) * s.tlas_cull_scale) * 0.9999f : 1.0f;
-        const float t_lo = fminf(t_min, 0.0f);
-        int stack[48]; int sp = 0;
-        int node = s.tlas_root;
-        for (;;) {
-            if (node >= 0) {
-                const float4* N = s.tlas_nodes + 4 * (size_t)node;
-                float4 n0 = HRT_LD4(N), n1 = HRT_LD4(N + 1), n2 = HRT_LD4(N + 2), n3 = HRT_LD4(N + 3);
-                float tn0, tf0, tn1, tf1;
-                slab2(n0, n1, n2, r.o, id, tn0, tf0, tn1, tf1);
-                if (COUNT) cnt->nodes += 2;
-                const float bound = cull_bound(b);
-                bool h0 = tn0 <= tf0 && tf0 >= t_lo && (tn0 <= 0.0f || tn0 * cull <= bound);
-                bool h1 = tn1 <= tf1 && tf1 >= t_lo && (tn1 <= 0.0f || tn1 * cull <= bound);
-                int c0 = float_as_int(n3.x), c1 = float_as_int(n3.y);
-                if (h0 && h1) {
-                    if (tn1 < tn0) { int tmp = c0; c0 = c1; c1 = tmp; }
-                    if (sp < 47) stack[sp++] = c1; else b.bad = 1;
-                    node = c0; continue;
-                }
-                if (h0) { node = c0; continue; }
-                if (h1) { node = c1; continue; }
-            } else {
-                object_hit_fast<COUNT>(s, ~node, r, t_min, b, key, bounce, cnt);
-            }
-            if (sp == 0 || b.bad) break;
-            node = stack[--sp];
-        }
-    }
-    need_ref = (!ok && s.n_objects > 0) || b.amb || b.bad;
-    Hit h; h.t = b.prim == HRT_MISS ? 0.0f : b.t; h.prim = b.prim; h.obj = b.obj; h.flags = 0;
-    return h;
-}
-
-template <bool COUNT>
-HRT_HDN inline Hit trace_fast(const DScene& s, const Ray& r, float t_min, float t_max, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
-{
-    bool need_ref = false;
-    Hit h = trace_fast_try<COUNT>(s, r, t_min, t_max, key, bounce, cnt, need_ref);
-    if (need_ref) {
-        if (COUNT) cnt->fallbacks += 1;
-        return trace_ref(s, r, t_min, t_max, key, bounce);
     }
     return h;
 }

@@ -1,16 +1,18 @@
-// hrt_kernels.cu — the sm_100a kernels of the wavefront path tracer and their launchers.
+// hrt_kernels.cu — the sm_100a kernels of the persistent-wavefront path tracer and their launchers.
 //
-//   K1 k_raygen          camera rays, Philox jitter                    (main.cpp:115-123, camera.h:32-39)
-//   K2 k_trace           closest hit per queued ray                    (world->hit, main.cpp:45)
-//      k_trace_retrace   rays whose answer depends on visiting order, in the reference's order (hrt_hit.cuh)
-//   K4 k_shade           hit record -> emitted + scatter / background; K3 = warp-ballot + one atomic per warp
-//                        appends the surviving rays to the next queue  (main.cpp:47-76, material.h, texture.cpp)
-//   K5 k_film_add / k_film_resolve   per-pixel sums in sample order, mean -> ACES -> sqrt -> 8 bit (film.cpp:25-52)
-//   K7 k_trace_batch / k_eval_batch  hit() on a caller-supplied ray batch (parity / micro-benchmark entry)
-//      k_render_mega     one thread per path, whole rayColour loop (validation of the wavefront pipeline)
+//   k_wave_init    K1: fills the first queue with camera paths (Philox jitter)      (main.cpp:115-123, camera.h:32-39)
+//   k_wave_trace   K2: closest hit per queued ray                                    (world->hit, main.cpp:45; hrt_trace.cuh)
+//   k_wave_shade   K4: hit record -> emitted + scatter / background                  (main.cpp:47-76, material.h, texture.cpp)
+//                  K3: warp-ballot + one atomic per warp appends the surviving rays to the front of the next queue;
+//                  K1: every finished path is replaced by a fresh camera path taken from a global counter (appended
+//                      from the back of the next queue), so the queue stays full until the image runs out of samples;
+//                  K5: a finished path adds its radiance to the fixed-point film (integer atomics: order independent)
+//   k_film_resolve K5: film -> float sums / mean -> ACES -> sqrt -> 8 bit            (main.cpp:126-131, film.cpp:25-52)
+//   k_trace_batch / k_eval_batch   K7: hit() on a caller-supplied ray batch (parity / micro-benchmark entry)
+//   k_render_mega  one thread per path, whole rayColour loop (validation of the wavefront pipeline)
 //
-// All kernels are persistent-style grid-stride loops over device-resident counts: the host never waits for a queue
-// length, a render is a fixed sequence of launches.  Compiled with -fmad=false (numerics contract, hrt_math.cuh).
+// All kernels are grid-stride loops over device-resident counts: the host never waits for a queue length.
+// Compiled with -fmad=false (numerics contract, hrt_math.cuh).
 #include <cuda_runtime.h>
 
 #include "hrt_kernels.h"
@@ -29,33 +31,14 @@ __device__ __forceinline__ RngKey make_key(uint64_t seed, uint32_t index, uint32
 }
 
 // ---- K7 ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(BLOCK) k_trace_batch(DScene s, const float4* __restrict__ rays, long long n, Hit* __restrict__ hits,
-                                                       uint64_t seed, unsigned int* __restrict__ retrace, unsigned int* __restrict__ n_retrace)
+__global__ void __launch_bounds__(BLOCK) k_trace_batch(DScene s, const float4* __restrict__ rays, long long n, Hit* __restrict__ hits, uint64_t seed)
 {
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         float4 a = __ldg(rays + 2 * i), b = __ldg(rays + 2 * i + 1);
         Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
         RngKey key = make_key(seed, (uint32_t)i, (uint32_t)(i >> 32), 0);
-        Hit h;
-        if (s.fast) {
-            bool need_ref = false;
-            h = trace_fast_try<false>(s, r, a.w, b.w, key, 0, nullptr, need_ref);
-            if (need_ref) { retrace[atomicAdd(n_retrace, 1u)] = (unsigned int)i; continue; }
-        } else h = trace_ref(s, r, a.w, b.w, key, 0);
-        hits[i] = h;
-    }
-}
-__global__ void __launch_bounds__(BLOCK) k_trace_batch_retrace(DScene s, const float4* __restrict__ rays, Hit* __restrict__ hits, uint64_t seed,
-                                                               const unsigned int* __restrict__ retrace, const unsigned int* __restrict__ n_retrace)
-{
-    const unsigned int n = *n_retrace;
-    for (unsigned int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
-        long long i = retrace[j];
-        float4 a = __ldg(rays + 2 * i), b = __ldg(rays + 2 * i + 1);
-        Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
-        RngKey key = make_key(seed, (uint32_t)i, (uint32_t)(i >> 32), 0);
-        hits[i] = trace_ref(s, r, a.w, b.w, key, 0);
+        hits[i] = s.fast ? trace_fast<false>(s, r, a.w, b.w, key, 0, nullptr) : trace_ref(s, r, a.w, b.w, key, 0);
     }
 }
 __global__ void __launch_bounds__(BLOCK) k_split_hits(const Hit* __restrict__ hits, long long n, uint32_t* __restrict__ prim, float* __restrict__ t)
@@ -84,147 +67,201 @@ __global__ void __launch_bounds__(BLOCK) k_eval_batch(DScene s, const float4* __
     }
 }
 
-// ---- K1 ---------------------------------------------------------------------------------------------------------------
-// path slot = s_local * npix + pixel; the slot is carried in ray.o.w
-__global__ void __launch_bounds__(BLOCK) k_raygen(RenderJob j, DCamera cam, int s_first, int s_count)
+// ---- film ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void film_add_channel(long long* px, int c, float v)
 {
-    const long long n = (long long)j.npix * s_count;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long slot = (long long)blockIdx.x * blockDim.x + threadIdx.x; slot < n; slot += stride) {
-        int pix = (int)(slot % j.npix), sl = (int)(slot / j.npix);
-        RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(s_first + sl), j.rng_mode);
-        Ray r = primary_ray(cam, j.width, j.height, pix, key);
-        j.rays[0][2 * slot] = make_float4(r.o.x, r.o.y, r.o.z, __int_as_float((int)slot));
-        j.rays[0][2 * slot + 1] = make_float4(r.d.x, r.d.y, r.d.z, 0.0f);
-        j.atten[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
-        j.radiance[slot] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0) j.counts[0] = (unsigned int)n;
+    if (v == 0.0f) return;
+    const float lim = (float)(1 << FILM_MAG_BITS);
+    if (v != v) { atomicOr((unsigned long long*)(px + 3), 1ull << (7 * c)); return; }
+    if (fabsf(v) > 3.402823466e+38f) { atomicOr((unsigned long long*)(px + 3), 1ull << (7 * (3 + c + (v < 0 ? 3 : 0)))); return; }
+    v = fminf(fmaxf(v, -lim), lim);
+    long long q = __float2ll_rn(v * (float)(1 << FILM_FRAC_BITS));             // power-of-two scale: exact, then one rounding
+    if (q != 0) atomicAdd((unsigned long long*)(px + c), (unsigned long long)q);
 }
-
-// ---- K2 ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(BLOCK) k_trace(DScene s, RenderJob j, int bounce, int s_first)
+__device__ __forceinline__ void film_add(long long* film, int pix, V3 c)
 {
-    const unsigned int n = j.counts[bounce];
-    const float4* __restrict__ rays = j.rays[bounce & 1];
-    const unsigned int stride = gridDim.x * blockDim.x;
-    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        float4 a = rays[2 * (size_t)i], b = rays[2 * (size_t)i + 1];
-        Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
-        int slot = __float_as_int(a.w);
-        RngKey key = make_key(j.seed, (uint32_t)(slot % j.npix), (uint32_t)(s_first + slot / j.npix), j.rng_mode);
-        Hit h;
-        if (s.fast) {
-            bool need_ref = false;
-            h = trace_fast_try<false>(s, r, j.t_min, hrt_inf(), key, (uint32_t)bounce, nullptr, need_ref);
-            if (need_ref) { j.retrace[atomicAdd(&j.n_retrace[bounce], 1u)] = i; continue; }
-        } else h = trace_ref(s, r, j.t_min, hrt_inf(), key, (uint32_t)bounce);
-        j.hits[i] = h;
-    }
+    long long* px = film + (size_t)pix * FILM_LANES;
+    film_add_channel(px, 0, c.x); film_add_channel(px, 1, c.y); film_add_channel(px, 2, c.z);
 }
-__global__ void __launch_bounds__(BLOCK) k_trace_retrace(DScene s, RenderJob j, int bounce, int s_first)
+__device__ __forceinline__ float film_channel(const long long* px, int c)
 {
-    const unsigned int n = j.n_retrace[bounce];
-    const float4* __restrict__ rays = j.rays[bounce & 1];
-    for (unsigned int q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x) {
-        unsigned int i = j.retrace[q];
-        float4 a = rays[2 * (size_t)i], b = rays[2 * (size_t)i + 1];
-        Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
-        int slot = __float_as_int(a.w);
-        RngKey key = make_key(j.seed, (uint32_t)(slot % j.npix), (uint32_t)(s_first + slot / j.npix), j.rng_mode);
-        j.hits[i] = trace_ref(s, r, j.t_min, hrt_inf(), key, (uint32_t)bounce);
-    }
+    const unsigned long long f = (unsigned long long)px[3];
+    const bool nan = (f >> (7 * c)) & 0x7f, pinf = (f >> (7 * (3 + c))) & 0x7f, ninf = (f >> (7 * (6 + c))) & 0x7f;
+    if (nan || (pinf && ninf)) return __int_as_float(0x7fc00000);
+    if (pinf) return hrt_inf();
+    if (ninf) return -hrt_inf();
+    return (float)((double)px[c] * (1.0 / (double)(1 << FILM_FRAC_BITS)));
 }
-
-// ---- K4 + K3 ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(BLOCK) k_shade(DScene s, RenderJob j, int bounce, int s_first, int last)
-{
-    const unsigned int n = j.counts[bounce];
-    const float4* __restrict__ rays = j.rays[bounce & 1];
-    float4* __restrict__ out = j.rays[(bounce + 1) & 1];
-    const unsigned int lane = threadIdx.x & 31u;
-    const unsigned int stride = gridDim.x * blockDim.x;
-    for (unsigned int base = blockIdx.x * blockDim.x + threadIdx.x - lane; base < n; base += stride) {
-        const unsigned int i = base + lane;
-        bool go = false; Ray r; int slot = 0;
-        if (i < n) {
-            float4 a = rays[2 * (size_t)i], b = rays[2 * (size_t)i + 1];
-            r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
-            slot = __float_as_int(a.w);
-            Hit h = j.hits[i];
-            RngKey key = make_key(j.seed, (uint32_t)(slot % j.npix), (uint32_t)(s_first + slot / j.npix), j.rng_mode);
-            float4 at4 = j.atten[slot];
-            V3 atten = v3(at4.x, at4.y, at4.z), rad;
-            go = shade_segment(s, h, r, atten, rad, key, (uint32_t)bounce);
-            if (rad.x != 0.0f || rad.y != 0.0f || rad.z != 0.0f) {               // result += attenuation * emitted / background
-                float4 acc = j.radiance[slot];
-                V3 sum = v3(acc.x, acc.y, acc.z) + rad;
-                j.radiance[slot] = make_float4(sum.x, sum.y, sum.z, 0.0f);
-            }
-            go = go && !last;                                                   // MAX_DEPTH reached: the partial sum stands (main.cpp:43,78)
-            if (go) j.atten[slot] = make_float4(atten.x, atten.y, atten.z, 0.0f);
-        }
-        const unsigned int m = __ballot_sync(0xffffffffu, go);
-        if (m) {
-            unsigned int pos = 0;
-            if (lane == 0) pos = atomicAdd(&j.counts[bounce + 1], (unsigned int)__popc(m));
-            pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1u));
-            if (go) {
-                out[2 * (size_t)pos] = make_float4(r.o.x, r.o.y, r.o.z, __int_as_float(slot));
-                out[2 * (size_t)pos + 1] = make_float4(r.d.x, r.d.y, r.d.z, 0.0f);
-            }
-        }
-    }
-}
-
-// ---- K5 ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(BLOCK) k_film_add(RenderJob j, int s_count, float* __restrict__ accum)
-{
-    for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < j.npix; pix += gridDim.x * blockDim.x) {
-        V3 sum = v3(accum[3 * (size_t)pix], accum[3 * (size_t)pix + 1], accum[3 * (size_t)pix + 2]);
-        for (int sl = 0; sl < s_count; ++sl) {                                  // fixed order: px += rayColour(...)  main.cpp:123
-            float4 c = j.radiance[(size_t)sl * j.npix + pix];
-            sum = sum + v3(c.x, c.y, c.z);
-        }
-        accum[3 * (size_t)pix] = sum.x; accum[3 * (size_t)pix + 1] = sum.y; accum[3 * (size_t)pix + 2] = sum.z;
-    }
-}
-__global__ void __launch_bounds__(BLOCK) k_film_resolve(const float* __restrict__ accum, int npix, int spp, float* __restrict__ mean, uint8_t* __restrict__ rgb8)
+__global__ void __launch_bounds__(BLOCK) k_film_resolve(const long long* __restrict__ film, int npix, int spp, float* __restrict__ sum,
+                                                        float* __restrict__ mean, uint8_t* __restrict__ rgb8)
 {
     for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += gridDim.x * blockDim.x) {
-        V3 c = v3(accum[3 * (size_t)pix], accum[3 * (size_t)pix + 1], accum[3 * (size_t)pix + 2]) / (float)spp;   // main.cpp:126
+        const long long* px = film + (size_t)pix * FILM_LANES;
+        V3 c = v3(film_channel(px, 0), film_channel(px, 1), film_channel(px, 2));
+        if (sum) { sum[3 * (size_t)pix] = c.x; sum[3 * (size_t)pix + 1] = c.y; sum[3 * (size_t)pix + 2] = c.z; }
+        c = c / (float)spp;                                                     // main.cpp:126
         if (mean) { mean[3 * (size_t)pix] = c.x; mean[3 * (size_t)pix + 1] = c.y; mean[3 * (size_t)pix + 2] = c.z; }
         if (rgb8) tonemap_write(c, rgb8 + 3 * (size_t)pix);
     }
 }
 
-// ---- megakernel ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(BLOCK) k_render_mega(DScene s, RenderJob j, DCamera cam, int s_first, int s_count)
+// ---- camera paths ---------------------------------------------------------------------------------------------------------
+// Path index p -> (local sample, pixel).  When the film is a whole number of 8x4 pixel tiles, 32 consecutive paths are
+// one tile of one sample, so a warp of fresh camera rays is a small screen-space block; otherwise pixels go in row order.
+__device__ __forceinline__ void path_pixel(const WaveJob& j, unsigned long long p, int& pix, int& sl)
 {
-    const long long n = (long long)j.npix * s_count;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long slot = (long long)blockIdx.x * blockDim.x + threadIdx.x; slot < n; slot += stride) {
-        int pix = (int)(slot % j.npix), sl = (int)(slot / j.npix);
-        RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(s_first + sl), j.rng_mode);
-        Ray r = primary_ray(cam, j.width, j.height, pix, key);
-        V3 atten = v3(1.0f), result = v3(0.0f);
-        for (int b = 0; b < j.max_depth; ++b) {
-            Hit h = s.fast ? trace_fast<false>(s, r, j.t_min, hrt_inf(), key, (uint32_t)b, nullptr) : trace_ref(s, r, j.t_min, hrt_inf(), key, (uint32_t)b);
-            V3 rad; bool go = shade_segment(s, h, r, atten, rad, key, (uint32_t)b);
-            result = result + rad;
-            if (!go) break;
-        }
-        j.radiance[slot] = make_float4(result.x, result.y, result.z, 0.0f);
+    sl = (int)(p / (unsigned long long)j.npix);
+    const unsigned int k = (unsigned int)(p - (unsigned long long)sl * (unsigned long long)j.npix);
+    if (j.tiles_x > 0) {
+        const unsigned int lane = k & 31u, tile = k >> 5;
+        const int x = (int)(tile % (unsigned int)j.tiles_x) * 8 + (int)(lane & 7u);
+        const int y = (int)(tile / (unsigned int)j.tiles_x) * 4 + (int)(lane >> 3);
+        pix = y * j.width + x;
+    } else pix = (int)k;
+}
+__device__ __forceinline__ unsigned int pack_state(int sl, int bounce, bool has_result)
+{ return ((unsigned int)sl << 8) | (unsigned int)bounce | (has_result ? 0x80000000u : 0u); }
+
+// writes the camera ray of path p into entry e of queue q
+__device__ __forceinline__ void write_camera_path(const WaveJob& j, const DCamera& cam, int q, unsigned int e, unsigned long long p)
+{
+    int pix, sl;
+    path_pixel(j, p, pix, sl);
+    RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + sl), j.rng_mode);
+    Ray r = primary_ray(cam, j.width, j.height, pix, key);
+    j.rays[q][2 * (size_t)e] = make_float4(r.o.x, r.o.y, r.o.z, __int_as_float(pix));
+    j.rays[q][2 * (size_t)e + 1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(pack_state(sl, 0, false)));
+    j.thr[q][e] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+}
+
+__device__ __forceinline__ unsigned long long min_ull(unsigned long long a, unsigned long long b) { return a < b ? a : b; }
+
+// ---- K1 (first fill) -------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(BLOCK) k_wave_init(WaveJob j, DCamera cam)
+{
+    const unsigned long long n = min_ull(j.ctl->total_paths, (unsigned long long)j.capacity);
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride)
+        write_camera_path(j, cam, 0, j.capacity - 1u - (unsigned int)p, p);
+}
+// runs after k_wave_init in stream order: publishes the first queue
+__global__ void k_wave_publish(WaveJob j)
+{
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        WaveCtl* c = j.ctl;
+        c->n_front[0] = 0; c->n_front[1] = 0; c->base[0] = 0; c->base[1] = 0;
+        c->next_path = min_ull(c->total_paths, (unsigned long long)j.capacity);
     }
 }
 
-__global__ void k_count_rays(const unsigned int* __restrict__ counts, const unsigned int* __restrict__ n_retrace, int max_depth, unsigned long long* __restrict__ totals)
+// entry index of thread slot i in a queue with n_front survivors: survivors first, then the regenerated paths
+__device__ __forceinline__ unsigned int entry_of(unsigned int i, unsigned int n_front, unsigned int capacity)
+{ return i < n_front ? i : capacity - 1u - (i - n_front); }
+
+// ---- K2 ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(BLOCK) k_wave_trace(DScene s, WaveJob j, int q)
 {
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        unsigned long long rays = 0, re = 0;
-        for (int b = 0; b < max_depth; ++b) { rays += counts[b]; re += n_retrace[b]; }
-        totals[0] += rays; totals[1] += re;
+    WaveCtl* c = j.ctl;
+    const unsigned int n_front = c->n_front[q];
+    const unsigned long long handed = min_ull(c->next_path, c->total_paths);
+    const unsigned int n = n_front + (unsigned int)(handed - c->base[q]);
+    if (blockIdx.x == 0 && threadIdx.x == 0) {     // nobody reads these in this kernel: prepare the queue the shade pass will fill
+        c->rays += n;
+        c->n_front[q ^ 1] = 0;
+        c->base[q ^ 1] = handed;
     }
+    const float4* __restrict__ rays = j.rays[q];
+    const unsigned int stride = gridDim.x * blockDim.x;
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const unsigned int e = entry_of(i, n_front, j.capacity);
+        float4 a = rays[2 * (size_t)e], b = rays[2 * (size_t)e + 1];
+        Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
+        const unsigned int st = __float_as_uint(b.w);
+        RngKey key = make_key(j.seed, (uint32_t)__float_as_int(a.w), (uint32_t)(j.s_first + (int)((st >> 8) & 0x7fffffu)), j.rng_mode);
+        j.hits[i] = s.fast ? trace_fast<false>(s, r, j.t_min, hrt_inf(), key, st & 0xffu, nullptr) : trace_ref(s, r, j.t_min, hrt_inf(), key, st & 0xffu);
+    }
+}
+
+// ---- K4 + K3 + K1 + K5 ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(BLOCK) k_wave_shade(DScene s, WaveJob j, DCamera cam, int q)
+{
+    WaveCtl* c = j.ctl;
+    const int o = q ^ 1;
+    const unsigned int n_front = c->n_front[q];
+    const unsigned long long base_out = c->base[o];                             // = paths handed out before this pass (set by k_wave_trace)
+    const unsigned int n = n_front + (unsigned int)(base_out - c->base[q]);
+    const unsigned long long total = c->total_paths;
+    const float4* __restrict__ rays = j.rays[q];
+    const unsigned int lane = threadIdx.x & 31u;
+    const unsigned int stride = gridDim.x * blockDim.x;
+    for (unsigned int base = blockIdx.x * blockDim.x + threadIdx.x - lane; base < n; base += stride) {
+        const unsigned int i = base + lane;
+        bool go = false, fresh = false; Ray r; V3 atten, result; int pix = 0; unsigned int st = 0; bool has_result = false;
+        if (i < n) {
+            const unsigned int e = entry_of(i, n_front, j.capacity);
+            float4 a = rays[2 * (size_t)e], b = rays[2 * (size_t)e + 1];
+            r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
+            pix = __float_as_int(a.w); st = __float_as_uint(b.w);
+            const Hit h = j.hits[i];
+            const unsigned int bounce = st & 0xffu; const int sl = (int)((st >> 8) & 0x7fffffu);
+            has_result = (st >> 31) != 0;
+            RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + sl), j.rng_mode);
+            float4 at4 = j.thr[q][e];
+            atten = v3(at4.x, at4.y, at4.z);
+            result = v3(0.0f);
+            if (has_result) { float4 r4 = j.res[q][e]; result = v3(r4.x, r4.y, r4.z); }
+            V3 rad;
+            go = shade_segment(s, h, r, atten, rad, key, bounce);
+            if (rad.x != 0.0f || rad.y != 0.0f || rad.z != 0.0f) { result = result + rad; has_result = true; }   // result += attenuation * emitted / background
+            go = go && (int)bounce + 1 < j.max_depth;                           // MAX_DEPTH reached: the partial sum stands (main.cpp:43,78)
+            if (go) st = pack_state(sl, (int)bounce + 1, has_result);
+            else {
+                if (has_result) film_add(j.film, pix, result);                  // px += rayColour(...)  main.cpp:123
+                fresh = true;
+            }
+        }
+        const unsigned int m_go = __ballot_sync(0xffffffffu, go), m_fresh = __ballot_sync(0xffffffffu, fresh);
+        unsigned int pos = 0; unsigned long long p0 = 0;
+        if (lane == 0) {
+            if (m_go) pos = atomicAdd(&c->n_front[o], (unsigned int)__popc(m_go));
+            if (m_fresh) p0 = atomicAdd(&c->next_path, (unsigned long long)__popc(m_fresh));
+        }
+        pos = __shfl_sync(0xffffffffu, pos, 0); p0 = __shfl_sync(0xffffffffu, p0, 0);
+        const unsigned int below = (1u << lane) - 1u;
+        if (go) {
+            const unsigned int e2 = pos + (unsigned int)__popc(m_go & below);
+            j.rays[o][2 * (size_t)e2] = make_float4(r.o.x, r.o.y, r.o.z, __int_as_float(pix));
+            j.rays[o][2 * (size_t)e2 + 1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(st));
+            j.thr[o][e2] = make_float4(atten.x, atten.y, atten.z, 0.0f);
+            if (has_result) j.res[o][e2] = make_float4(result.x, result.y, result.z, 0.0f);
+        } else if (fresh) {
+            const unsigned long long p = p0 + (unsigned long long)__popc(m_fresh & below);
+            if (p < total) write_camera_path(j, cam, o, j.capacity - 1u - (unsigned int)(p - base_out), p);
+        }
+    }
+}
+
+// ---- megakernel ------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(BLOCK) k_render_mega(DScene s, WaveJob j, DCamera cam)
+{
+    const unsigned long long n = (unsigned long long)j.npix * (unsigned long long)j.s_count;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    unsigned long long rays = 0;
+    for (unsigned long long p = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride) {
+        int pix, sl; path_pixel(j, p, pix, sl);
+        RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + sl), j.rng_mode);
+        Ray r = primary_ray(cam, j.width, j.height, pix, key);
+        V3 atten = v3(1.0f), result = v3(0.0f); bool has_result = false;
+        for (int b = 0; b < j.max_depth; ++b) {
+            Hit h = s.fast ? trace_fast<false>(s, r, j.t_min, hrt_inf(), key, (uint32_t)b, nullptr) : trace_ref(s, r, j.t_min, hrt_inf(), key, (uint32_t)b);
+            ++rays;
+            V3 rad; bool go = shade_segment(s, h, r, atten, rad, key, (uint32_t)b);
+            if (rad.x != 0.0f || rad.y != 0.0f || rad.z != 0.0f) { result = result + rad; has_result = true; }
+            if (!go) break;
+        }
+        if (has_result) film_add(j.film, pix, result);
+    }
+    if (rays) atomicAdd(&j.ctl->rays, rays);
 }
 
 int grid_for(long long n, int sm_count, int per_sm)
@@ -238,13 +275,9 @@ int grid_for(long long n, int sm_count, int per_sm)
 } // namespace
 
 // ---- launchers -------------------------------------------------------------------------------------------------------------
-void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed,
-                        unsigned int* d_retrace, unsigned int* d_n_retrace, int sm_count, cudaStream_t st, uint64_t* launches)
+void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed, int sm_count, cudaStream_t st, uint64_t* launches)
 {
-    cudaMemsetAsync(d_n_retrace, 0, sizeof(unsigned int), st);
-    k_trace_batch<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed, d_retrace, d_n_retrace);
-    *launches += 1;
-    if (s.fast) { k_trace_batch_retrace<<<sm_count * 4, BLOCK, 0, st>>>(s, d_rays, d_hits, seed, d_retrace, d_n_retrace); *launches += 1; }
+    k_trace_batch<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed); *launches += 1;
 }
 void launch_split_hits(const Hit* d_hits, long long n, uint32_t* d_prim, float* d_t, int sm_count, cudaStream_t st, uint64_t* launches)
 {
@@ -256,33 +289,27 @@ void launch_eval_batch(const DScene& s, const float4* d_rays, const Hit* d_hits,
     k_eval_batch<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, d_rays, d_hits, n, d_normal, d_uv, d_front); *launches += 1;
 }
 
-void launch_render_batch(const DScene& s, const RenderJob& j, const DCamera& cam, int s_first, int s_count, float* d_accum,
-                         bool mega, int sm_count, cudaStream_t st, uint64_t* launches, cudaEvent_t* ev_trace, cudaEvent_t* ev_shade)
+void launch_wave_init(const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches)
 {
-    const long long n = (long long)j.npix * s_count;
-    const int g = grid_for(n, sm_count, 16);
-    if (mega) {
-        k_render_mega<<<g, BLOCK, 0, st>>>(s, j, cam, s_first, s_count); *launches += 1;
-    } else {
-        cudaMemsetAsync(j.counts, 0, sizeof(unsigned int) * (size_t)(j.max_depth + 1), st);
-        cudaMemsetAsync(j.n_retrace, 0, sizeof(unsigned int) * (size_t)(j.max_depth + 1), st);
-        k_raygen<<<g, BLOCK, 0, st>>>(j, cam, s_first, s_count); *launches += 1;
-        for (int b = 0; b < j.max_depth; ++b) {
-            if (ev_trace) cudaEventRecord(ev_trace[2 * b], st);
-            k_trace<<<g, BLOCK, 0, st>>>(s, j, b, s_first); *launches += 1;
-            if (s.fast) { k_trace_retrace<<<sm_count * 4, BLOCK, 0, st>>>(s, j, b, s_first); *launches += 1; }
-            if (ev_trace) cudaEventRecord(ev_trace[2 * b + 1], st);
-            k_shade<<<g, BLOCK, 0, st>>>(s, j, b, s_first, b == j.max_depth - 1 ? 1 : 0); *launches += 1;
-            if (ev_shade) cudaEventRecord(ev_shade[b], st);
-        }
-        k_count_rays<<<1, 32, 0, st>>>(j.counts, j.n_retrace, j.max_depth, j.totals); *launches += 1;
-    }
-    k_film_add<<<grid_for(j.npix, sm_count, 16), BLOCK, 0, st>>>(j, s_count, d_accum); *launches += 1;
+    k_wave_init<<<grid_for((long long)j.capacity, sm_count, 16), BLOCK, 0, st>>>(j, cam);
+    k_wave_publish<<<1, 32, 0, st>>>(j);
+    *launches += 2;
 }
-
-void launch_film_resolve(const float* d_accum, int npix, int spp, float* d_mean, uint8_t* d_rgb8, int sm_count, cudaStream_t st, uint64_t* launches)
+void launch_wave_trace(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches)
 {
-    k_film_resolve<<<grid_for(npix, sm_count, 16), BLOCK, 0, st>>>(d_accum, npix, spp, d_mean, d_rgb8); *launches += 1;
+    k_wave_trace<<<grid_for((long long)j.capacity, sm_count, 16), BLOCK, 0, st>>>(s, j, it & 1); *launches += 1;
+}
+void launch_wave_shade(const DScene& s, const WaveJob& j, const DCamera& cam, int it, int sm_count, cudaStream_t st, uint64_t* launches)
+{
+    k_wave_shade<<<grid_for((long long)j.capacity, sm_count, 16), BLOCK, 0, st>>>(s, j, cam, it & 1); *launches += 1;
+}
+void launch_render_mega(const DScene& s, const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches)
+{
+    k_render_mega<<<grid_for((long long)j.npix * j.s_count, sm_count, 16), BLOCK, 0, st>>>(s, j, cam); *launches += 1;
+}
+void launch_film_resolve(const long long* d_film, int npix, int spp, float* d_sum, float* d_mean, uint8_t* d_rgb8, int sm_count, cudaStream_t st, uint64_t* launches)
+{
+    k_film_resolve<<<grid_for(npix, sm_count, 16), BLOCK, 0, st>>>(d_film, npix, spp, d_sum, d_mean, d_rgb8); *launches += 1;
 }
 
 } // namespace hrt

@@ -9,38 +9,61 @@ namespace hrt {
 
 struct Hit;
 
-// Device-resident working set of one wavefront batch of `capacity` paths (path slot = s_local * npix + pixel).
-//   rays[2]   : ping-pong ray queues, 2 x float4 per ray: (o.xyz, slot) (d.xyz, -)            32 B / ray
-//   hits      : one 16-byte Hit per queue entry, written by K2, read by K4
-//   atten     : per path slot, rayColour's `attenuation` (main.cpp:40)                         16 B / path
-//   radiance  : per path slot, rayColour's `result`                                            16 B / path
-//   counts[b] : queue length at bounce b (counts[b+1] is appended to by K4 of bounce b)
-//   retrace   : queue entries whose answer depends on the visiting order (hrt_hit.cuh), n_retrace[b] of them
-struct RenderJob {
+// Film: order-independent sample accumulation.  Per pixel four int64 lanes: lanes 0-2 hold the r, g, b sample SUMS in
+// fixed point (units of 2^-FILM_FRAC_BITS, each sample rounded to nearest and clamped to +-2^FILM_MAG_BITS), lane 3 holds
+// nine 7-bit fields "a NaN / +inf / -inf sample was added to channel c" (set with atomicOr locally, so <= 1 per rank;
+// a cross-rank integer SUM keeps them non-zero).  Integer addition commutes, so the film does not depend on the order
+// in which paths finish, on the wavefront capacity or on how samples are split over GPUs.
+constexpr int FILM_LANES = 4;
+constexpr int FILM_FRAC_BITS = 26;
+constexpr int FILM_MAG_BITS = 21;
+
+// Device-resident control block of one persistent-wavefront render call.
+struct WaveCtl {
+    unsigned int n_front[2];            // queue q: survivors, compacted from the front
+    unsigned long long base[2];         // queue q: value of `next_path` when the shade pass that fills q started
+    unsigned long long next_path;       // next camera path index to hand out (may overshoot total_paths)
+    unsigned long long total_paths;
+    unsigned long long rays;            // closest-hit queries issued
+    unsigned long long pad;
+};
+
+// Working set of a render call.  Queue entry e of queue q (capacity entries each):
+//   rays[q][2e]   = (o.xyz, pixel index)            rays[q][2e+1] = (d.xyz, has_result << 31 | sample_local << 8 | bounce)
+//   thr[q][e]     = (rayColour's currentAttenuation, -)           res[q][e] = (rayColour's `result`, -) when has_result
+// Survivors of a shade pass are appended from the front [0, n_front); regenerated camera paths take slots from the back
+// (path p of that pass sits at capacity - 1 - (p - base)), so incoherent secondary rays and coherent primary rays stay in
+// separate warps.  hits[e] is written by the trace pass for the entry order of that pass.
+struct WaveJob {
     int width, height, npix;
+    int tiles_x, tiles_y;               // 8x4 pixel tiles; a path index is (sample_local * tiles + tile) * 32 + lane
     int max_depth;
     float t_min;
     uint64_t seed;
     int rng_mode;
+    int s_first, s_count;
+    unsigned int capacity;
     float4* rays[2];
+    float4* thr[2];
+    float4* res[2];
     Hit* hits;
-    float4* atten;
-    float4* radiance;
-    unsigned int* counts;
-    unsigned int* retrace;
-    unsigned int* n_retrace;
-    unsigned long long* totals;     // [0] rays traced, [1] rays re-traced in reference order
+    WaveCtl* ctl;
+    long long* film;                    // npix * FILM_LANES
 };
 
-void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed,
-                        unsigned int* d_retrace, unsigned int* d_n_retrace, int sm_count, cudaStream_t st, uint64_t* launches);
+void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_split_hits(const Hit* d_hits, long long n, uint32_t* d_prim, float* d_t, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_eval_batch(const DScene& s, const float4* d_rays, const Hit* d_hits, long long n, float* d_normal, float* d_uv, uint8_t* d_front,
                        int sm_count, cudaStream_t st, uint64_t* launches);
-// one batch of s_count samples per pixel: raygen, max_depth x (trace, retrace, shade), film add into d_accum.
-// ev_trace (2 per bounce) / ev_shade (1 per bounce) are optional CUDA events recorded around the kernels.
-void launch_render_batch(const DScene& s, const RenderJob& j, const DCamera& cam, int s_first, int s_count, float* d_accum,
-                         bool mega, int sm_count, cudaStream_t st, uint64_t* launches, cudaEvent_t* ev_trace, cudaEvent_t* ev_shade);
-void launch_film_resolve(const float* d_accum, int npix, int spp, float* d_mean, uint8_t* d_rgb8, int sm_count, cudaStream_t st, uint64_t* launches);
+
+// persistent wavefront: init fills queue 0, then iteration `it` is trace(queue it&1) + shade(queue it&1 -> queue (it+1)&1)
+void launch_wave_init(const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches);
+void launch_wave_trace(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches);
+void launch_wave_shade(const DScene& s, const WaveJob& j, const DCamera& cam, int it, int sm_count, cudaStream_t st, uint64_t* launches);
+// one thread per path, whole rayColour loop (validation of the wavefront pipeline); same film
+void launch_render_mega(const DScene& s, const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches);
+
+// film -> per-pixel float sums (may be null) / mean (may be null) / 8-bit tonemapped image (may be null)
+void launch_film_resolve(const long long* d_film, int npix, int spp, float* d_sum, float* d_mean, uint8_t* d_rgb8, int sm_count, cudaStream_t st, uint64_t* launches);
 
 } // namespace hrt

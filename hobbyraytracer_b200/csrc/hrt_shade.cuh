@@ -4,7 +4,7 @@
 // this file with the reference is statistical; the arithmetic is kept in the reference's order and precision
 // (including its double-precision spots) so that the only difference is the random stream and libm.
 #pragma once
-#include "hrt_hit.cuh"
+#include "hrt_trace.cuh"
 
 namespace hrt {
 

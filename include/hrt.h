@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define HRT_ABI_VERSION 1
+#define HRT_ABI_VERSION 2
 
 /* ---- error codes --------------------------------------------------------------------------- */
 #define HRT_OK            0
@@ -110,7 +110,7 @@ typedef struct hrt_render_params {
     int32_t  flags;          /* HRT_RENDER_* bits                                                    */
 } hrt_render_params;
 
-#define HRT_RENDER_MEGAKERNEL 1   /* one thread per path instead of the wavefront pipeline (debug/validation) */
+#define HRT_RENDER_MEGAKERNEL 1   /* one thread per path instead of the persistent wavefront (debug/validation) */
 
 typedef struct hrt_stats {
     uint64_t rays;            /* closest-hit queries issued (= world->hit calls of main.cpp:45)      */
@@ -122,8 +122,7 @@ typedef struct hrt_stats {
     double   ms_total;        /* device time of the whole call                                       */
     uint64_t node_tests;      /* only filled by counters-enabled entry points                        */
     uint64_t prim_tests;
-    uint64_t retraced;        /* rays whose answer depended on the visiting order and were re-traced in the
-                                 reference's order (HRT_BVH_SAH only)                                   */
+    uint64_t retraced;        /* reserved (the ordered traversal resolves order-dependent rays in place)   */
     uint64_t scene_bytes;     /* bytes of scene data resident in device memory after hrt_scene_commit  */
     double   ms_build;        /* host time of the BVH builds in hrt_scene_commit                       */
 } hrt_stats;
@@ -183,12 +182,20 @@ int hrt_trace_batch_device(hrt_scene* s, const void* d_rays, int64_t n, void* d_
  * samples (NULL to skip); out_rgb8: width*height*3 bytes = Film::tonemap + writeColour of sum/spp
  * (film.cpp:25-52), row 0 = top row as in the reference's pixel buffer (NULL to skip). */
 int hrt_render(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, float* out_sum, uint8_t* out_rgb8);
-/* Device variants for multi-GPU use: accumulate sample sums into a device buffer of width*height*3 floats
- * (the caller zeroes it and may NCCL-reduce it), then resolve a summed buffer to 8-bit / mean. */
+/* Device variants for multi-GPU use.  The FILM is a device buffer of hrt_film_bytes(width, height) bytes:
+ * per pixel four int64 lanes — the r, g, b sample sums in fixed point (2^-26 units; every sample rounded to
+ * nearest and clamped to +-2^21) and one lane of "a NaN / +inf / -inf sample was added" fields.  Integer sums
+ * commute: the film does not depend on the order in which paths finish nor on how the samples were split over
+ * GPUs, so an integer SUM reduction of the films of all ranks (ncclSum on int64) gives bit-identical images for
+ * any GPU count.  The caller zeroes the film; hrt_render_accumulate_device adds sample indices
+ * [sample_first, sample_first + sample_count) of every pixel; hrt_film_resolve_device turns a (reduced) film
+ * into float sums / float means (sum / spp, main.cpp:126) / the 8-bit image (film.cpp:25-52), any of which
+ * may be NULL. */
+int hrt_film_bytes(int width, int height);
 int hrt_render_accumulate_device(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
-                                 void* d_accum, void* stream);
-int hrt_film_resolve_device(hrt_scene* s, const void* d_accum, int width, int height, int spp,
-                            void* d_mean_or_null, void* d_rgb8_or_null, void* stream);
+                                 void* d_film, void* stream);
+int hrt_film_resolve_device(hrt_scene* s, const void* d_film, int width, int height, int spp,
+                            void* d_sum_or_null, void* d_mean_or_null, void* d_rgb8_or_null, void* stream);
 
 int hrt_get_stats(hrt_scene* s, hrt_stats* out);
 int hrt_reset_stats(hrt_scene* s);

@@ -36,7 +36,7 @@ template <class F> void parallel_for(int64_t n, int64_t chunk, F&& fn)
 }
 } // namespace
 
-struct hsim_scene { HostScene host; HostUp up; DScene d{}; TraceCounters cnt{0, 0, 0}; };
+struct hsim_scene { HostScene host; HostUp up; DScene d{}; TraceCounters cnt{0, 0, 0, 0, 0}; };
 
 #define B(call) do { int rc = (call); return rc; } while (0)
 
@@ -72,14 +72,14 @@ int hsim_trace_batch(hsim_scene* s, const float* rays, int64_t n, uint32_t* prim
                      float* normal, float* uv, uint8_t* front, uint64_t rng_seed)
 {
     if (!s->host.committed) { g_err = "scene not committed"; return HRT_ERR_STATE; }
-    std::atomic<unsigned long long> nodes(0), prims(0), fb(0);
+    std::atomic<unsigned long long> nodes(0), prims(0), fb(0), amb(0), bad(0);
     parallel_for(n, 4096, [&](int64_t i) {
         const float* q = rays + i * 8;
         Ray r; r.o = v3(q[0], q[1], q[2]); r.d = v3(q[4], q[5], q[6]);
         RngKey key; key.k0 = (uint32_t)rng_seed; key.k1 = (uint32_t)(rng_seed >> 32); key.index = (uint32_t)i; key.sample = (uint32_t)(i >> 32); key.mode = 0;
-        TraceCounters c{0, 0, 0};
+        TraceCounters c{0, 0, 0, 0, 0};
         Hit h = s->d.fast ? trace_fast<true>(s->d, r, q[3], q[7], key, 0, &c) : trace_ref(s->d, r, q[3], q[7], key, 0);
-        nodes += c.nodes; prims += c.prims; fb += c.fallbacks;
+        nodes += c.nodes; prims += c.prims; fb += c.fallbacks; amb += c.amb; bad += c.bad;
         bool hit = h.prim != HRT_MISS;
         prim_id[i] = h.prim; t[i] = hit ? h.t : 0.0f;
         if (normal || uv || front) {
@@ -90,10 +90,11 @@ int hsim_trace_batch(hsim_scene* s, const float* rays, int64_t n, uint32_t* prim
             if (front) front[i] = hit ? (rec.front ? 1 : 0) : 0;
         }
     });
-    s->cnt.nodes = nodes; s->cnt.prims = prims; s->cnt.fallbacks = fb;
+    s->cnt.nodes = nodes; s->cnt.prims = prims; s->cnt.fallbacks = fb; s->cnt.amb = amb; s->cnt.bad = bad;
     return 0;
 }
 int hsim_counters(hsim_scene* s, uint64_t* out3) { out3[0] = s->cnt.nodes; out3[1] = s->cnt.prims; out3[2] = s->cnt.fallbacks; return 0; }
+int hsim_counters5(hsim_scene* s, uint64_t* out5) { out5[0] = s->cnt.nodes; out5[1] = s->cnt.prims; out5[2] = s->cnt.fallbacks; out5[3] = s->cnt.amb; out5[4] = s->cnt.bad; return 0; }
 
 // render(): per-pixel sums of rayColour over `spp` samples, one path at a time (what the megakernel does)
 int hsim_render(hsim_scene* s, const hrt_camera* cam, const hrt_render_params* p, float* out_sum, uint8_t* out_rgb8)

@@ -195,19 +195,56 @@ def test_wavefront_equals_megakernel_and_sample_split(hrt, cache_dir):
         wf, _ = g.render(c, w, h, spp, seed=9)
         mk, _ = g.render(c, w, h, spp, seed=9, flags=abi.RENDER_MEGAKERNEL)
         assert np.array_equal(bits(wf), bits(mk)), "wavefront pipeline differs from the one-thread-per-path loop"
-        # samples are keyed by (pixel, global sample index): any split into calls / batches gives the same sums
-        os.environ["HRT_BATCH_PATHS"] = str(w * h * 5)
-        try:
-            wf2, _ = g.render(c, w, h, spp, seed=9)
-        finally:
-            del os.environ["HRT_BATCH_PATHS"]
-        assert np.array_equal(bits(wf), bits(wf2))
+        # samples are keyed by (pixel, global sample index) and the film adds integers: the wavefront capacity (hence the
+        # order in which paths start and finish) does not change a single bit
+        for cap in (1024, 5000):
+            os.environ["HRT_WAVE_CAPACITY"] = str(cap)
+            try:
+                wf2, _ = g.render(c, w, h, spp, seed=9)
+            finally:
+                del os.environ["HRT_WAVE_CAPACITY"]
+            assert np.array_equal(bits(wf), bits(wf2))
         a, _ = g.render(c, w, h, spp, seed=9, sample_first=0, sample_count=10, want_rgb8=False)
         b, _ = g.render(c, w, h, spp, seed=9, sample_first=10, sample_count=14, want_rgb8=False)
         assert np.allclose(a + b, wf, rtol=1e-5, atol=1e-6)
     ref = sd.build(hrt, abi.BVH_REFERENCE, 3).render(c, w, h, spp, seed=9)[0]
     fast = sd.build(hrt, abi.BVH_SAH, 3).render(c, w, h, spp, seed=9)[0]
     assert np.array_equal(bits(ref), bits(fast)), "SAH-order render differs from reference-order render"
+
+
+def test_film_is_split_invariant(hrt, cache_dir):
+    """The multi-GPU contract on one GPU: films of disjoint sample ranges added as integers (what the NCCL reduce does)
+    equal the film of one call over all samples, bit for bit, and so do the resolved images."""
+    import torch
+    from hobbyraytracer_b200 import multigpu
+    sd, cam, _ = scenes.teapot_scene(cache_dir, n=24, env_w=128, env_h=64)
+    w, h, spp = 96, 64, 20                      # 96 x 64: whole 8x4 tiles; the odd size below takes the row-order mapping
+    c = scenes.camera_for(cam, w, h)
+    g = sd.build(hrt, abi.BVH_SAH, 3)
+    whole = multigpu.new_film(hrt, w, h)
+    multigpu.render_split(g, c, w, h, spp, whole, 0, 1, None, seed=5)
+    for world in (2, 3, 8):
+        parts = torch.zeros_like(whole)
+        for rank in range(world):
+            f = multigpu.new_film(hrt, w, h)
+            first, count = multigpu.sample_range(spp, rank, world)
+            p = abi.RenderParams(w, h, spp, first, count, 50, 0.001, 5, 0, 0)
+            import ctypes as C
+            hrt.check(hrt.fn("render_accumulate_device")(g.h, C.byref(c), C.byref(p), f.data_ptr(), None), "render_accumulate_device")
+            torch.cuda.synchronize()
+            parts += f
+        assert torch.equal(parts, whole), f"film differs for a {world}-way sample split"
+    rgb = torch.zeros(w * h * 3, dtype=torch.uint8, device="cuda"); tot = torch.zeros(w * h * 3, dtype=torch.float32, device="cuda")
+    hrt.check(hrt.fn("film_resolve_device")(g.h, whole.data_ptr(), w, h, spp, tot.data_ptr(), None, rgb.data_ptr(), None), "film_resolve_device")
+    torch.cuda.synchronize()
+    S, B = g.render(c, w, h, spp, seed=5)
+    assert np.array_equal(bits(S.reshape(-1)), bits(tot.cpu().numpy())) and np.array_equal(B.reshape(-1), rgb.cpu().numpy())
+    # a film that is not a whole number of tiles
+    w2, h2 = 61, 37
+    c2 = scenes.camera_for(cam, w2, h2)
+    a, _ = g.render(c2, w2, h2, 6, seed=3)
+    b, _ = g.render(c2, w2, h2, 6, seed=3, flags=abi.RENDER_MEGAKERNEL)
+    assert np.array_equal(bits(a), bits(b)) and np.isfinite(a).all() and a.mean() > 0
 
 
 def test_large_batch_orders_agree(hrt, cache_dir):

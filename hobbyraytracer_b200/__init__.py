@@ -18,6 +18,10 @@ def load() -> "abi.Lib":
     """Bind csrc/libhrt_b200.so.  Raises HrtError when the library is missing (build with __graft_entry__.build())."""
     global _lib
     if _lib is None:
+        so = os.environ.get("HRT_PRODUCT_SO", PRODUCT_SO)      # A/B builds of the same CUDA library (tuning experiments)
+        if so != PRODUCT_SO:
+            _lib = abi.Lib(so, "hrt_")
+            return _lib
         if not os.path.exists(PRODUCT_SO):
             raise abi.HrtError(f"{PRODUCT_SO} is not built; run `python -c 'import __graft_entry__ as g; g.build()'` "
                                "(there is no CPU fallback)")

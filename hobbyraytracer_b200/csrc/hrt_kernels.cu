@@ -159,7 +159,10 @@ __device__ __forceinline__ unsigned int entry_of(unsigned int i, unsigned int n_
 { return i < n_front ? i : capacity - 1u - (i - n_front); }
 
 // ---- K2 ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(BLOCK) k_wave_trace(DScene s, WaveJob j, int q)
+#ifndef HRT_TRACE_MIN_BLOCKS
+#define HRT_TRACE_MIN_BLOCKS 8      // 64 registers: +10 % over 128 registers / 4 blocks on shiny_teapot (A/B on B200, profiles/README.md)
+#endif
+__global__ void __launch_bounds__(BLOCK, HRT_TRACE_MIN_BLOCKS) k_wave_trace(DScene s, WaveJob j, int q)
 {
     WaveCtl* c = j.ctl;
     const unsigned int n_front = c->n_front[q];
@@ -183,8 +186,13 @@ __global__ void __launch_bounds__(BLOCK) k_wave_trace(DScene s, WaveJob j, int q
 }
 
 // ---- K4 + K3 + K1 + K5 ------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(BLOCK) k_wave_shade(DScene s, WaveJob j, DCamera cam, int q)
+// One queue-slot claim per BLOCK and pass of the loop (two returning atomics on two hot addresses): a per-warp claim
+// made every warp wait ~1.5 us for the round trip to L2 and serialised 260 k same-address atomics per pass (profiles/ r1b).
+constexpr int SHADE_BLOCK = 256;
+__global__ void __launch_bounds__(SHADE_BLOCK) k_wave_shade(DScene s, WaveJob j, DCamera cam, int q)
 {
+    __shared__ unsigned int w_go[SHADE_BLOCK / 32], w_fresh[SHADE_BLOCK / 32];
+    __shared__ unsigned int s_pos; __shared__ unsigned long long s_p0;
     WaveCtl* c = j.ctl;
     const int o = q ^ 1;
     const unsigned int n_front = c->n_front[q];
@@ -192,11 +200,12 @@ __global__ void __launch_bounds__(BLOCK) k_wave_shade(DScene s, WaveJob j, DCame
     const unsigned int n = n_front + (unsigned int)(base_out - c->base[q]);
     const unsigned long long total = c->total_paths;
     const float4* __restrict__ rays = j.rays[q];
-    const unsigned int lane = threadIdx.x & 31u;
-    const unsigned int stride = gridDim.x * blockDim.x;
-    for (unsigned int base = blockIdx.x * blockDim.x + threadIdx.x - lane; base < n; base += stride) {
-        const unsigned int i = base + lane;
+    const unsigned int lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const unsigned int stride = gridDim.x * SHADE_BLOCK;
+    for (unsigned int base = blockIdx.x * SHADE_BLOCK; base < n; base += stride) {
+        const unsigned int i = base + threadIdx.x;
         bool go = false, fresh = false; Ray r; V3 atten, result; int pix = 0; unsigned int st = 0; bool has_result = false;
+        r.o = v3(0.0f); r.d = v3(0.0f); atten = v3(0.0f); result = v3(0.0f);
         if (i < n) {
             const unsigned int e = entry_of(i, n_front, j.capacity);
             float4 a = rays[2 * (size_t)e], b = rays[2 * (size_t)e + 1];
@@ -208,7 +217,6 @@ __global__ void __launch_bounds__(BLOCK) k_wave_shade(DScene s, WaveJob j, DCame
             RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + sl), j.rng_mode);
             float4 at4 = j.thr[q][e];
             atten = v3(at4.x, at4.y, at4.z);
-            result = v3(0.0f);
             if (has_result) { float4 r4 = j.res[q][e]; result = v3(r4.x, r4.y, r4.z); }
             V3 rad;
             go = shade_segment(s, h, r, atten, rad, key, bounce);
@@ -221,23 +229,28 @@ __global__ void __launch_bounds__(BLOCK) k_wave_shade(DScene s, WaveJob j, DCame
             }
         }
         const unsigned int m_go = __ballot_sync(0xffffffffu, go), m_fresh = __ballot_sync(0xffffffffu, fresh);
-        unsigned int pos = 0; unsigned long long p0 = 0;
-        if (lane == 0) {
-            if (m_go) pos = atomicAdd(&c->n_front[o], (unsigned int)__popc(m_go));
-            if (m_fresh) p0 = atomicAdd(&c->next_path, (unsigned long long)__popc(m_fresh));
+        if (lane == 0) { w_go[warp] = (unsigned int)__popc(m_go); w_fresh[warp] = (unsigned int)__popc(m_fresh); }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned int t_go = 0, t_fresh = 0;
+#pragma unroll
+            for (int w = 0; w < SHADE_BLOCK / 32; ++w) { unsigned int g = w_go[w], f = w_fresh[w]; w_go[w] = t_go; w_fresh[w] = t_fresh; t_go += g; t_fresh += f; }
+            s_pos = t_go ? atomicAdd(&c->n_front[o], t_go) : 0u;
+            s_p0 = t_fresh ? atomicAdd(&c->next_path, (unsigned long long)t_fresh) : 0ull;
         }
-        pos = __shfl_sync(0xffffffffu, pos, 0); p0 = __shfl_sync(0xffffffffu, p0, 0);
+        __syncthreads();
         const unsigned int below = (1u << lane) - 1u;
         if (go) {
-            const unsigned int e2 = pos + (unsigned int)__popc(m_go & below);
+            const unsigned int e2 = s_pos + w_go[warp] + (unsigned int)__popc(m_go & below);
             j.rays[o][2 * (size_t)e2] = make_float4(r.o.x, r.o.y, r.o.z, __int_as_float(pix));
             j.rays[o][2 * (size_t)e2 + 1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(st));
             j.thr[o][e2] = make_float4(atten.x, atten.y, atten.z, 0.0f);
             if (has_result) j.res[o][e2] = make_float4(result.x, result.y, result.z, 0.0f);
         } else if (fresh) {
-            const unsigned long long p = p0 + (unsigned long long)__popc(m_fresh & below);
+            const unsigned long long p = s_p0 + (unsigned long long)(w_fresh[warp] + (unsigned int)__popc(m_fresh & below));
             if (p < total) write_camera_path(j, cam, o, j.capacity - 1u - (unsigned int)(p - base_out), p);
         }
+        __syncthreads();                                                        // the next pass of the loop rewrites the shared counters
     }
 }
 
@@ -301,7 +314,10 @@ void launch_wave_trace(const DScene& s, const WaveJob& j, int it, int sm_count, 
 }
 void launch_wave_shade(const DScene& s, const WaveJob& j, const DCamera& cam, int it, int sm_count, cudaStream_t st, uint64_t* launches)
 {
-    k_wave_shade<<<grid_for((long long)j.capacity, sm_count, 16), BLOCK, 0, st>>>(s, j, cam, it & 1); *launches += 1;
+    {
+    long long want = ((long long)j.capacity + SHADE_BLOCK - 1) / SHADE_BLOCK, cap = (long long)sm_count * 8;
+    k_wave_shade<<<(int)(want < cap ? want : cap), SHADE_BLOCK, 0, st>>>(s, j, cam, it & 1); *launches += 1;
+    }
 }
 void launch_render_mega(const DScene& s, const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches)
 {

@@ -147,16 +147,20 @@ HRT_HDN inline bool mat_scatter(const DScene& s, int mat, const Ray& rin, const 
     return false;
 }
 
-// background lookup of rayColour, main.cpp:47-58 (atan2 / acos and the +0.5 are double there)
+// background lookup of rayColour, main.cpp:47-58.  The reference's unqualified atan2 / acos resolve to the double
+// overloads and are rounded back to float; here they are the fp32 functions (<= 2 ulp from that value), which moves a
+// nearest-texel lookup only when u or v sits within 2 ulp of a texel boundary.  Transcendentals are outside the bit-exact
+// contract; the +0.5 stays a double add like main.cpp:55.
 HRT_HDN inline V3 background_colour(const DScene& s, const Ray& r)
 {
+    if (s.background < 0) return v3(0.0f);
+    if (s.textures[s.background].kind == TEX_SOLID) return tex_value(s, s.background, 0.0f, 0.0f, v3(0.0f));
     V3 nD = normalize(r.d);
-    float phi = (float)atan2((double)nD.z, (double)nD.x);
-    float theta = (float)acos((double)nD.y);
+    float phi = atan2f(nD.z, nD.x);
+    float theta = acosf(nD.y);
     const float pi = 3.14159265358979323846264338327950288f;
     float u = (float)((double)(phi / (2 * pi)) + 0.5);
     float v = theta / pi;
-    if (s.background < 0) return v3(0.0f);
     return tex_value(s, s.background, u, v, v3(0.0f));
 }
 

@@ -197,6 +197,14 @@ HRT_HDN inline void object_walk(const DScene& s, int i, const Ray& r, float t_mi
         if (m.ref_root < 0) return;
         Ray lr = to_local(s, ob, r);
         if (!dir_ok(lr.d) || !(hrt_finite(lr.o.x) && hrt_finite(lr.o.y) && hrt_finite(lr.o.z))) { b.bad = 1; return; }
+        if (m.fast_root >= 0) {          // whole-mesh rejection before any per-ray triangle set-up: most camera rays miss the mesh
+            const V3 id = v3(1.0f / lr.d.x, 1.0f / lr.d.y, 1.0f / lr.d.z);
+            const float4* N = m.fast_nodes + 4 * (size_t)m.fast_root;
+            float tn0, tf0, tn1, tf1;
+            slab2(HRT_LD4(N), HRT_LD4(N + 1), HRT_LD4(N + 2), lr.o, id, tn0, tf0, tn1, tf1);
+            const float t_lo = fminf(t_min, 0.0f);
+            if (!(tn0 <= tf0 && tf0 >= t_lo) && !(tn1 <= tf1 && tf1 >= t_lo)) return;
+        }
         const int kZ = tri_kz(lr.o);
         if (!COLLECT && !shear_ok(lr, kZ)) { b.shear = 1; return; }             // pass 2 will collect every hit along this ray
         switch (kZ) {
@@ -298,28 +306,43 @@ HRT_HDN inline bool replay(const DScene& s, const Ray& r, float t_min, float t_m
 }
 
 // ---- closest hit ---------------------------------------------------------------------------------------------------------------
+#if defined(__CUDACC__)
+#define HRT_COLD __host__ __device__ __noinline__
+#else
+#define HRT_COLD __attribute__((noinline))
+#endif
+
+// cold path, kept out of line so that the hot kernel body is pass 1 only: pass 2 + replay, or trace_ref as the last resort
 template <bool COUNT>
-HRT_HDN inline Hit trace_fast(const DScene& s, const Ray& r, float t_min, float t_max, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
+HRT_COLD Hit trace_resolve(const DScene& s, const Ray& r, float t_min, float t_max, const RngKey& key, uint32_t bounce, TraceCounters* cnt,
+                           int bad, int shear, float beta)
+{
+    Hit h; h.t = 0.0f; h.prim = HRT_MISS; h.obj = -1; h.flags = 0;
+    if (!bad) {
+        if (COUNT) cnt->amb += 1;
+        Best b; b.t = 0.0f; b.a = 0.0f; b.prim = HRT_MISS; b.obj = -1; b.amb = 0; b.bad = 0; b.shear = 0; b.t_max = t_max;
+        Collector k; k.n = 0; k.overflow = 0; k.bad = 0;
+        k.beta = shear ? t_max : beta;
+        world_walk<true, COUNT>(s, r, t_min, b, k, key, bounce, cnt);
+        if (!k.overflow && !k.bad && !b.bad && replay(s, r, t_min, t_max, k, key, bounce, h)) return h;
+    }
+    if (COUNT) { cnt->fallbacks += 1; cnt->bad += 1; }
+    return trace_ref(s, r, t_min, t_max, key, bounce);
+}
+
+template <bool COUNT>
+HRT_HD Hit trace_fast(const DScene& s, const Ray& r, float t_min, float t_max, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
 {
     Hit h; h.t = 0.0f; h.prim = HRT_MISS; h.obj = -1; h.flags = 0;
     if (s.n_objects <= 0) return h;
     const bool ok = dir_ok(r.d) && hrt_finite(r.o.x) && hrt_finite(r.o.y) && hrt_finite(r.o.z);
+    Best b; b.t = 0.0f; b.a = 0.0f; b.prim = HRT_MISS; b.obj = -1; b.amb = 0; b.bad = ok ? 0 : 1; b.shear = 0; b.t_max = t_max;
     if (ok) {
-        Best b; b.t = 0.0f; b.a = 0.0f; b.prim = HRT_MISS; b.obj = -1; b.amb = 0; b.bad = 0; b.shear = 0; b.t_max = t_max;
-        Collector k; k.n = 0;
-        world_walk<false, COUNT>(s, r, t_min, b, k, key, bounce, cnt);
+        Collector* none = nullptr;
+        world_walk<false, COUNT>(s, r, t_min, b, *none, key, bounce, cnt);       // pass 1 never touches the collector
         if (!b.bad && !b.amb && !b.shear) { h.t = b.prim == HRT_MISS ? 0.0f : b.t; h.prim = b.prim; h.obj = b.obj; return h; }
-        if (!b.bad) {
-            if (COUNT) cnt->amb += 1;
-            k.n = 0; k.overflow = 0; k.bad = 0;
-            k.beta = b.shear ? t_max : cull_bound(b);
-            b.bad = 0;
-            world_walk<true, COUNT>(s, r, t_min, b, k, key, bounce, cnt);
-            if (!k.overflow && !k.bad && !b.bad && replay(s, r, t_min, t_max, k, key, bounce, h)) return h;
-        }
     }
-    if (COUNT) { cnt->fallbacks += 1; cnt->bad += 1; }
-    return trace_ref(s, r, t_min, t_max, key, bounce);
+    return trace_resolve<COUNT>(s, r, t_min, t_max, key, bounce, cnt, b.bad, b.shear, cull_bound(b));
 }
 
 } // namespace hrt

@@ -263,7 +263,7 @@ def run_own(args):
                            "cache": "the wavefront queues (4 Mi entries: rays + hits + path state = 600 MB) exceed the 126 MB L2 and are rewritten every pass; no flush needed"},
                 "e2e": {"value": float(e2e_r.item()) / float(e2e_s.item()) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": scene_bytes,
                         "d2h_bytes_per_step": npix * 15, "steps": e2e_steps, "includes": "scene build + BVH build + upload, render, float film + 8-bit image read-back"},
-                "gpu_launches": int(launches), "commit_s": t_commit,
+                "gpu_launches": int(launches), "commit_s": t_commit, "replayed_fraction": float(st.retraced) / max(float(st.rays), 1.0), "ref_walk_rays": int(st.prim_tests),
                 "kernel_ms": {"trace": st.ms_trace, "shade": st.ms_shade, "other": st.ms_other, "total": st.ms_total, "note": "rank 0, CUDA events inside the timed region"},
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": (ach / peak) if ach else None, "traffic": traffic,
                              "kernel": "k_wave_trace", "alg_bytes_per_ray": b_alg, "peak_source": peak_src,

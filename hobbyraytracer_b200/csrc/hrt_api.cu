@@ -10,7 +10,7 @@
 #include <string>
 #include <vector>
 
-#include "hrt_trace.cuh"
+#include "hrt_shade.cuh"
 #include "hrt_kernels.h"
 #include "hrt_upload.h"
 
@@ -208,7 +208,12 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
     fin = s->h_ctl[0];
     float ms = 0; CK(cudaEventElapsedTime(&ms, ev_begin, ev_end));
     s->stats.ms_total += ms;
-    s->stats.rays += fin.rays;
+    s->stats.rays += fin.rays; s->stats.retraced += fin.resolved; s->stats.prim_tests += fin.fallbacks;
+    if (fin.fallbacks && getenv("HRT_DEBUG_FALLBACK"))
+        for (unsigned long long k = 0; k < fin.fallbacks && k < 16; ++k) {
+            const float* g = fin.dbg[k]; unsigned int st; memcpy(&st, &g[7], 4); int pix; memcpy(&pix, &g[3], 4);
+            fprintf(stderr, "fallback ray: o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g) pixel %d bounce %u\n", g[0], g[1], g[2], g[4], g[5], g[6], pix, st & 0xffu);
+        }
     s->stats.ms_other = s->stats.ms_total - s->stats.ms_trace - s->stats.ms_shade;
     return 0;
 }

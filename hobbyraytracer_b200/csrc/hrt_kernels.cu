@@ -68,29 +68,19 @@ __global__ void __launch_bounds__(BLOCK) k_eval_batch(DScene s, const float4* __
 }
 
 // ---- film ---------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void film_add_channel(long long* px, int c, float v)
-{
-    if (v == 0.0f) return;
-    const float lim = (float)(1 << FILM_MAG_BITS);
-    if (v != v) { atomicOr((unsigned long long*)(px + 3), 1ull << (7 * c)); return; }
-    if (fabsf(v) > 3.402823466e+38f) { atomicOr((unsigned long long*)(px + 3), 1ull << (7 * (3 + c + (v < 0 ? 3 : 0)))); return; }
-    v = fminf(fmaxf(v, -lim), lim);
-    long long q = __float2ll_rn(v * (float)(1 << FILM_FRAC_BITS));             // power-of-two scale: exact, then one rounding
-    if (q != 0) atomicAdd((unsigned long long*)(px + c), (unsigned long long)q);
-}
+// quantisation / flag fields / reconstruction live in hrt_shade.cuh (shared with the CPU simulation harness)
 __device__ __forceinline__ void film_add(long long* film, int pix, V3 c)
 {
     long long* px = film + (size_t)pix * FILM_LANES;
-    film_add_channel(px, 0, c.x); film_add_channel(px, 1, c.y); film_add_channel(px, 2, c.z);
-}
-__device__ __forceinline__ float film_channel(const long long* px, int c)
-{
-    const unsigned long long f = (unsigned long long)px[3];
-    const bool nan = (f >> (7 * c)) & 0x7f, pinf = (f >> (7 * (3 + c))) & 0x7f, ninf = (f >> (7 * (6 + c))) & 0x7f;
-    if (nan || (pinf && ninf)) return __int_as_float(0x7fc00000);
-    if (pinf) return hrt_inf();
-    if (ninf) return -hrt_inf();
-    return (float)((double)px[c] * (1.0 / (double)(1 << FILM_FRAC_BITS)));
+    const float v[3] = {c.x, c.y, c.z};
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+        if (v[ch] == 0.0f) continue;
+        long long q; unsigned long long flag;
+        film_quantize(v[ch], ch, q, flag);
+        if (flag) atomicOr((unsigned long long*)(px + 3), flag);
+        else if (q != 0) atomicAdd((unsigned long long*)(px + ch), (unsigned long long)q);
+    }
 }
 __global__ void __launch_bounds__(BLOCK) k_film_resolve(const long long* __restrict__ film, int npix, int spp, float* __restrict__ sum,
                                                         float* __restrict__ mean, uint8_t* __restrict__ rgb8)
@@ -181,7 +171,12 @@ __global__ void __launch_bounds__(BLOCK, HRT_TRACE_MIN_BLOCKS) k_wave_trace(DSce
         Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
         const unsigned int st = __float_as_uint(b.w);
         RngKey key = make_key(j.seed, (uint32_t)__float_as_int(a.w), (uint32_t)(j.s_first + (int)((st >> 8) & 0x7fffffu)), j.rng_mode);
-        j.hits[i] = s.fast ? trace_fast<false>(s, r, j.t_min, hrt_inf(), key, st & 0xffu, nullptr) : trace_ref(s, r, j.t_min, hrt_inf(), key, st & 0xffu);
+        const Hit h = s.fast ? trace_fast<false>(s, r, j.t_min, hrt_inf(), key, st & 0xffu, nullptr) : trace_ref(s, r, j.t_min, hrt_inf(), key, st & 0xffu);
+        if (h.flags & (HIT_RESOLVED | HIT_FALLBACK)) {
+            const unsigned long long k = atomicAdd((h.flags & HIT_FALLBACK) ? &c->fallbacks : &c->resolved, 1ull);
+            if ((h.flags & HIT_FALLBACK) && k < 16) { float* g = c->dbg[k]; g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w; g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w; }
+        }
+        j.hits[i] = h;
     }
 }
 

@@ -9,14 +9,7 @@ namespace hrt {
 
 struct Hit;
 
-// Film: order-independent sample accumulation.  Per pixel four int64 lanes: lanes 0-2 hold the r, g, b sample SUMS in
-// fixed point (units of 2^-FILM_FRAC_BITS, each sample rounded to nearest and clamped to +-2^FILM_MAG_BITS), lane 3 holds
-// nine 7-bit fields "a NaN / +inf / -inf sample was added to channel c" (set with atomicOr locally, so <= 1 per rank;
-// a cross-rank integer SUM keeps them non-zero).  Integer addition commutes, so the film does not depend on the order
-// in which paths finish, on the wavefront capacity or on how samples are split over GPUs.
-constexpr int FILM_LANES = 4;
-constexpr int FILM_FRAC_BITS = 26;
-constexpr int FILM_MAG_BITS = 21;
+// Film layout and arithmetic: hrt_shade.cuh (FILM_LANES, film_quantize, film_channel).
 
 // Device-resident control block of one persistent-wavefront render call.
 struct WaveCtl {
@@ -25,7 +18,10 @@ struct WaveCtl {
     unsigned long long next_path;       // next camera path index to hand out (may overshoot total_paths)
     unsigned long long total_paths;
     unsigned long long rays;            // closest-hit queries issued
+    unsigned long long resolved;        // rays answered by pass 2 + replay (hrt_trace.cuh)
+    unsigned long long fallbacks;       // rays answered by trace_ref
     unsigned long long pad;
+    float dbg[16][8];                   // first rays that took the trace_ref fallback (o, pixel, d, state), for diagnosis
 };
 
 // Working set of a render call.  Queue entry e of queue q (capacity entries each):

@@ -216,4 +216,40 @@ HRT_HD void tonemap_write(V3 c, uint8_t* px)
     px[2] = (uint8_t)(256 * cmin(cmax(q.z, 0.0f), 0.9999f));
 }
 
+// ---- film: order-independent sample accumulation ---------------------------------------------------------------------------
+// Per pixel four int64 lanes: lanes 0-2 hold the r, g, b sample SUMS in fixed point (units of 2^-FILM_FRAC_BITS, each
+// sample rounded to nearest and clamped to +-2^FILM_MAG_BITS), lane 3 holds nine 7-bit fields "a NaN / +inf / -inf
+// sample was added to channel c" (set with an atomic OR locally, so <= 1 per rank; a cross-rank integer SUM of up to
+// 127 ranks keeps them non-zero).  Integer addition commutes, so the film does not depend on the order in which paths
+// finish, on the wavefront capacity or on how samples are split over GPUs.  The reference sums floats in sample order
+// (main.cpp:123); with 26 fractional bits the rounding of one sample is <= 7.5e-9 absolute, below fp32's own rounding
+// of a running sum >= 0.25, and unbiased.
+constexpr int FILM_LANES = 4;
+constexpr int FILM_FRAC_BITS = 26;
+constexpr int FILM_MAG_BITS = 21;
+
+HRT_HD void film_quantize(float v, int ch, long long& q, unsigned long long& flag)
+{
+    q = 0; flag = 0;
+    if (v != v) { flag = 1ull << (7 * ch); return; }
+    if (fabsf(v) > 3.402823466e+38f) { flag = 1ull << (7 * (3 + ch + (v < 0 ? 3 : 0))); return; }
+    const float lim = (float)(1 << FILM_MAG_BITS);
+    v = v < -lim ? -lim : (v > lim ? lim : v);
+    const float scaled = v * (float)(1 << FILM_FRAC_BITS);                      // power-of-two scale: exact
+#if defined(__CUDA_ARCH__)
+    q = __float2ll_rn(scaled);
+#else
+    q = (long long)nearbyintf(scaled);                                          // round-to-nearest-even, like cvt.rni
+#endif
+}
+HRT_HD float film_channel(const long long* px, int ch)
+{
+    const unsigned long long f = (unsigned long long)px[3];
+    const bool nan = ((f >> (7 * ch)) & 0x7f) != 0, pinf = ((f >> (7 * (3 + ch))) & 0x7f) != 0, ninf = ((f >> (7 * (6 + ch))) & 0x7f) != 0;
+    if (nan || (pinf && ninf)) return int_as_float(0x7fc00000);
+    if (pinf) return hrt_inf();
+    if (ninf) return -hrt_inf();
+    return (float)((double)px[ch] * (1.0 / (double)(1 << FILM_FRAC_BITS)));
+}
+
 } // namespace hrt

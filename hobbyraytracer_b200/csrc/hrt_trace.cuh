@@ -29,6 +29,8 @@ constexpr float NEAR_EPS = 1e-5f;            // relative distance under which tw
 constexpr float CULL_MARGIN = 0.0625f;       // pass 1 keeps everything that starts within 6.25 % beyond the best candidate
 constexpr float SHEAR_LIMIT = 64.0f;         // max|d| / |d[kZ]| above which ITriangle's t is too inaccurate to cull by
 constexpr float SLAB_WIDEN = 4.76837158e-7f; // 2^-21: widening of the SAH-node slab interval (conservative vs aabb.h)
+constexpr int HIT_RESOLVED = 2;              // Hit::flags: answer came from pass 2 + replay
+constexpr int HIT_FALLBACK = 4;              // Hit::flags: answer came from trace_ref (last resort)
 constexpr int KMAX = 16;                     // candidates a replay can hold
 
 struct TraceCounters { unsigned long long nodes, prims, fallbacks, amb, bad; };
@@ -324,10 +326,12 @@ HRT_COLD Hit trace_resolve(const DScene& s, const Ray& r, float t_min, float t_m
         Collector k; k.n = 0; k.overflow = 0; k.bad = 0;
         k.beta = shear ? t_max : beta;
         world_walk<true, COUNT>(s, r, t_min, b, k, key, bounce, cnt);
-        if (!k.overflow && !k.bad && !b.bad && replay(s, r, t_min, t_max, k, key, bounce, h)) return h;
+        if (!k.overflow && !k.bad && !b.bad && replay(s, r, t_min, t_max, k, key, bounce, h)) { h.flags |= HIT_RESOLVED; return h; }
     }
     if (COUNT) { cnt->fallbacks += 1; cnt->bad += 1; }
-    return trace_ref(s, r, t_min, t_max, key, bounce);
+    h = trace_ref(s, r, t_min, t_max, key, bounce);
+    h.flags |= HIT_FALLBACK;
+    return h;
 }
 
 template <bool COUNT>
@@ -335,6 +339,14 @@ HRT_HD Hit trace_fast(const DScene& s, const Ray& r, float t_min, float t_max, c
 {
     Hit h; h.t = 0.0f; h.prim = HRT_MISS; h.obj = -1; h.flags = 0;
     if (s.n_objects <= 0) return h;
+    if (r.o.x != r.o.x && r.o.y != r.o.y && r.o.z != r.o.z) {
+        // A path whose hit point became NaN (a NaN-t hit) keeps bouncing until MAX_DEPTH.  With an
+        // all-NaN origin every comparison in every hit() is false, so every slab test passes and every primitive accepts
+        // with t = NaN; the reference walks the whole scene and ends with the LAST primitive in its order.  Same answer,
+        // without the walk (a whole-scene reference walk costs milliseconds of single-thread latency per pass here).
+        if (s.nan_obj >= 0) { h.t = int_as_float(0x7fc00000); h.prim = s.nan_prim; h.obj = s.nan_obj; }
+        return h;
+    }
     const bool ok = dir_ok(r.d) && hrt_finite(r.o.x) && hrt_finite(r.o.y) && hrt_finite(r.o.z);
     Best b; b.t = 0.0f; b.a = 0.0f; b.prim = HRT_MISS; b.obj = -1; b.amb = 0; b.bad = ok ? 0 : 1; b.shear = 0; b.t_max = t_max;
     if (ok) {

@@ -2,6 +2,7 @@
 // where the bytes live for the consumer: a cudaMalloc'ed copy in the product (hrt_api.cu), the host pointer itself
 // in the CPU simulation harness (tests/hostsim).
 #pragma once
+#include <cstring>
 #include <vector>
 
 #include "hrt_host.h"
@@ -53,6 +54,18 @@ DScene make_dscene(HostScene& s, Up& up)
     d.background = s.background;
     d.fast = fast ? 1 : 0;
     d.tlas_cull_scale = s.tlas_cull_scale;
+    d.nan_obj = -1; d.nan_prim = HRT_MISS;
+    for (int i = (int)s.d_objects.size() - 1; i >= 0 && d.nan_obj < 0; --i) {
+        const DObject& ob = s.d_objects[(size_t)i];
+        if (ob.medium) { d.nan_obj = i; d.nan_prim = ob.medium_prim; }           // (an empty-mesh boundary never hits, see below)
+        else if (ob.kind == SHAPE_BOX) { d.nan_obj = i; d.nan_prim = ob.prim_base + 5u; }
+        else if (ob.kind != SHAPE_MESH) { d.nan_obj = i; d.nan_prim = ob.prim_base; }
+        if (ob.kind == SHAPE_MESH) {                                             // last triangle of the left-then-right walk (bvh.cpp:69-78)
+            const HostShape& sh = s.shapes[(size_t)s.mesh_shapes[(size_t)ob.mesh]];
+            if (sh.ref.root < 0 || sh.leaves.empty()) { d.nan_obj = -1; d.nan_prim = HRT_MISS; continue; }
+            if (!ob.medium) { int tr; std::memcpy(&tr, &sh.leaves[sh.leaves.size() - 7].w, 4); d.nan_obj = i; d.nan_prim = ob.prim_base + (uint32_t)tr; }
+        }
+    }
     return d;
 }
 

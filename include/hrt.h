@@ -120,9 +120,10 @@ typedef struct hrt_stats {
     double   ms_shade;        /* device time in the shading / regeneration kernel                    */
     double   ms_other;        /* raygen, film, resets                                                */
     double   ms_total;        /* device time of the whole call                                       */
-    uint64_t node_tests;      /* only filled by counters-enabled entry points                        */
-    uint64_t prim_tests;
-    uint64_t retraced;        /* reserved (the ordered traversal resolves order-dependent rays in place)   */
+    uint64_t node_tests;      /* reserved                                                            */
+    uint64_t prim_tests;      /* rays answered by the last-resort reference-order walk (NaN t, zero direction components) */
+    uint64_t retraced;        /* rays whose answer depended on the visiting order and was settled by replaying the
+                                 reference's sequential process over the collected candidates (HRT_BVH_SAH only) */
     uint64_t scene_bytes;     /* bytes of scene data resident in device memory after hrt_scene_commit  */
     double   ms_build;        /* host time of the BVH builds in hrt_scene_commit                       */
 } hrt_stats;

@@ -7,6 +7,8 @@
 // include/hrt.h with the prefix hsim_.  The product library never links or loads this file; nothing here is a
 // fallback for the CUDA path.
 #include <atomic>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <limits>
@@ -113,6 +115,7 @@ int hsim_render(hsim_scene* s, const hrt_camera* cam, const hrt_render_params* p
             V3 atten = v3(1.0f), result = v3(0.0f);
             for (int b = 0; b < max_depth; ++b) {
                 Hit hh = s->d.fast ? trace_fast<false>(s->d, r, t_min, hrt_inf(), key, (uint32_t)b, nullptr) : trace_ref(s->d, r, t_min, hrt_inf(), key, (uint32_t)b);
+                if ((hh.flags & HIT_FALLBACK) && getenv("HSIM_DEBUG")) fprintf(stderr, "fallback ray bounce %d o=(%.9g %.9g %.9g) d=(%.9g %.9g %.9g)\n", b, r.o.x, r.o.y, r.o.z, r.d.x, r.d.y, r.d.z);
                 V3 rad; bool go = shade_segment(s->d, hh, r, atten, rad, key, (uint32_t)b);
                 result = result + rad;
                 if (!go) break;
@@ -122,6 +125,56 @@ int hsim_render(hsim_scene* s, const hrt_camera* cam, const hrt_render_params* p
         if (out_sum) { out_sum[pidx * 3] = sum.x; out_sum[pidx * 3 + 1] = sum.y; out_sum[pidx * 3 + 2] = sum.z; }
         if (out_rgb8) tonemap_write(sum / (float)p->spp, out_rgb8 + pidx * 3);
     });
+    return 0;
+}
+
+// The film entry points of include/hrt.h on host memory (same fixed-point arithmetic as the kernels, hrt_shade.cuh):
+// what the multi-GPU driver (hobbyraytracer_b200/multigpu.py) calls, so its sample split + integer reduce can be run
+// on CPU tensors over gloo.
+int hsim_film_bytes(int width, int height) { return width * height * FILM_LANES * (int)sizeof(long long); }
+int hsim_render_accumulate_device(hsim_scene* s, const hrt_camera* cam, const hrt_render_params* p, void* film_, void*)
+{
+    if (!s->host.committed) { g_err = "scene not committed"; return HRT_ERR_STATE; }
+    long long* film = (long long*)film_;
+    DCamera c = make_camera(*cam);
+    const int w = p->width, h = p->height;
+    const int first = p->sample_first, count = p->sample_count > 0 ? p->sample_count : p->spp;
+    const int max_depth = p->max_depth > 0 ? p->max_depth : 50;
+    const float t_min = p->t_min > 0 ? p->t_min : 0.001f;
+    parallel_for((int64_t)w * h, 256, [&](int64_t pidx) {
+        long long* px = film + pidx * FILM_LANES;
+        for (int sidx = first; sidx < first + count; ++sidx) {
+            RngKey key; key.k0 = (uint32_t)p->seed; key.k1 = (uint32_t)(p->seed >> 32); key.index = (uint32_t)pidx; key.sample = (uint32_t)sidx; key.mode = p->rng_mode;
+            Ray r = primary_ray(c, w, h, (int)pidx, key);
+            V3 atten = v3(1.0f), result = v3(0.0f);
+            for (int b = 0; b < max_depth; ++b) {
+                Hit hh = s->d.fast ? trace_fast<false>(s->d, r, t_min, hrt_inf(), key, (uint32_t)b, nullptr) : trace_ref(s->d, r, t_min, hrt_inf(), key, (uint32_t)b);
+                V3 rad; bool go = shade_segment(s->d, hh, r, atten, rad, key, (uint32_t)b);
+                if (rad.x != 0.0f || rad.y != 0.0f || rad.z != 0.0f) result = result + rad;
+                if (!go) break;
+            }
+            const float v[3] = {result.x, result.y, result.z};
+            for (int ch = 0; ch < 3; ++ch) {
+                if (v[ch] == 0.0f) continue;
+                long long q; unsigned long long flag; film_quantize(v[ch], ch, q, flag);
+                if (flag) px[3] = (long long)((unsigned long long)px[3] | flag); else px[ch] += q;
+            }
+        }
+    });
+    return 0;
+}
+int hsim_film_resolve_device(hsim_scene*, const void* film_, int width, int height, int spp, void* sum_, void* mean_, void* rgb8_, void*)
+{
+    const long long* film = (const long long*)film_;
+    float* sum = (float*)sum_; float* mean = (float*)mean_; uint8_t* rgb8 = (uint8_t*)rgb8_;
+    for (int64_t pix = 0; pix < (int64_t)width * height; ++pix) {
+        const long long* px = film + pix * FILM_LANES;
+        V3 c = v3(film_channel(px, 0), film_channel(px, 1), film_channel(px, 2));
+        if (sum) { sum[3 * pix] = c.x; sum[3 * pix + 1] = c.y; sum[3 * pix + 2] = c.z; }
+        c = c / (float)spp;
+        if (mean) { mean[3 * pix] = c.x; mean[3 * pix + 1] = c.y; mean[3 * pix + 2] = c.z; }
+        if (rgb8) tonemap_write(c, rgb8 + 3 * pix);
+    }
     return 0;
 }
 

@@ -256,3 +256,17 @@ def test_large_batch_orders_agree(hrt, cache_dir):
     b = sd.build(hrt, abi.BVH_SAH, 3).trace(rays, extras=False)
     assert np.array_equal(a["prim"], b["prim"]) and np.array_equal(bits(a["t"]), bits(b["t"]))
     assert (a["prim"] != abi.MISS).mean() > 0.15
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_nan_rays(orc, hrt, mode):
+    """Rays left behind by NaN-t hits (all-NaN origin: answered without a walk) and partially non-finite rays
+    (reference-order walk) agree with the oracle, which is pinned to the reference on the same rays."""
+    from test_hostsim_vs_oracle import nan_rays
+    cases = [spheres_scene(), rects_scene(), mesh_scene(8), mesh_scene(8, ops=OPS[4])]
+    sd, _, _ = scenes.cornell_smoke_scene(glass_sphere=False); cases.append(sd)
+    for sd in cases:
+        o = sd.build(orc, 0, 5); g = sd.build(hrt, mode, 5)
+        rays = nan_rays()
+        ro, rg = o.trace(rays, rng_seed=3, extras=False), g.trace(rays, rng_seed=3, extras=False)
+        assert np.array_equal(ro["prim"], rg["prim"]) and np.array_equal(bits(ro["t"]), bits(rg["t"]))

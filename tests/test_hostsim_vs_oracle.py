@@ -221,3 +221,34 @@ def test_media_boundaries(orc, hsim):
     o2 = sd2.build(orc, 0, 5)
     for mode in (abi.BVH_REFERENCE, abi.BVH_SAH):
         check_hits(o2.trace(rays), sd2.build(hsim, mode, 5).trace(rays))
+
+
+def nan_rays(n=64, seed=0):
+    """Rays a NaN-t hit leaves behind (origin NaN in all components; direction finite, NaN or zero), plus partially
+    non-finite rays that must take the reference-order walk."""
+    rng = np.random.default_rng(seed)
+    r = np.empty((n, 8), F); r[:, 3] = 1e-3; r[:, 7] = np.inf
+    r[:, 0:3] = np.nan
+    r[:, 4:7] = rng.normal(size=(n, 3))
+    r[n // 4: n // 2, 4:7] = np.nan
+    r[n // 2: 5 * n // 8, 4:7] = 0
+    k = 3 * n // 4
+    r[k:, 0:3] = rng.normal(size=(n - k, 3)) + np.array([0, 1, 0])      # partially non-finite from here on
+    r[k::3, 0] = np.nan; r[k + 1::3, 1] = np.inf; r[k + 2::3, 5] = np.nan
+    return r
+
+
+@pytest.mark.parametrize("mode", [abi.BVH_REFERENCE, abi.BVH_SAH])
+def test_nan_rays(orc, hsim, mode):
+    """An all-NaN origin makes every primitive accept (all comparisons false): the reference ends with the last one in
+    its visiting order.  The ordered traversal answers that without walking the scene."""
+    cases = [spheres_scene(), rects_scene(), mesh_scene(8), mesh_scene(8, ops=OPS[4]), mesh_scene(8, ops=OPS[3], with_floor=False)]
+    sd, _, _ = scenes.cornell_smoke_scene(glass_sphere=False); cases.append(sd)          # last object is a medium
+    sd = mesh_scene(8); m = sd.material(abi.MAT_LAMBERTIAN, (0.5, 0.5, 0.5))
+    pos, nrm, uv = scenes.blob_mesh(2, 2, 1.0, 0.0, seed=1); sd.add(sd.mesh(pos[:0], nrm[:0], uv[:0], m)); cases.append(sd)   # last object: empty mesh
+    for sd in cases:
+        o = sd.build(orc, 0, 5); h = sd.build(hsim, mode, 5)
+        rays = nan_rays()
+        ro, rh = o.trace(rays, rng_seed=3, extras=False), h.trace(rays, rng_seed=3, extras=False)
+        assert np.array_equal(ro["prim"], rh["prim"]) and np.array_equal(bits(ro["t"]), bits(rh["t"]))
+        assert (ro["prim"][:32] != abi.MISS).all()

@@ -135,6 +135,25 @@ def test_mesh_degenerate_rays(orc, ref):
     assert same_bits(ro["t"], rr["t"])
 
 
+def test_nan_origin_rays(orc, ref):
+    """What a NaN-t hit leaves behind: rays whose origin is NaN.  Every comparison in hit() is false, so the reference
+    accepts every primitive and ends with the last one in its visiting order; the oracle must agree (the CUDA path
+    answers these without walking the scene, hrt_trace.cuh)."""
+    from test_hostsim_vs_oracle import nan_rays
+    sd = _mesh_scene(8)
+    m = sd.material(abi.MAT_LAMBERTIAN, (0.5, 0.5, 0.5))
+    sd.add(sd.sphere((0.5, 0.5, 0.5), 0.25, m)); sd.add(sd.box((0, 1, 0), (1.5, 2, 1), m))
+    for extra in (None, "mesh_last"):
+        if extra:
+            pos, nrm, uv = scenes.blob_mesh(6, 6, 1.0, 0.2, seed=5, center=(1, 1, 0)); sd.add(sd.mesh(pos, nrm, uv, m), [(abi.XF_TRANSLATE, (0.5, 0, 0))])
+        o, r = both(sd, orc, ref)
+        rays = nan_rays()
+        ro, rr = o.trace(rays), r.trace(rays)
+        assert np.array_equal(ro["prim"], rr["prim"]) and np.array_equal(np.isnan(ro["t"]), np.isnan(rr["t"]))
+        assert same_bits(np.nan_to_num(ro["t"], nan=0.0), np.nan_to_num(rr["t"], nan=0.0))
+        assert (ro["prim"][:32] != abi.MISS).all() and len(set(ro["prim"][:32].tolist())) == 1
+
+
 @pytest.mark.parametrize("ops", [
     [(abi.XF_TRANSLATE, (0.5, -0.25, 1.0))],
     [(abi.XF_SCALE, (1.5, 0.5, 2.0))],

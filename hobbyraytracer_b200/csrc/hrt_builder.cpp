@@ -42,7 +42,8 @@ int b_add_texture_env(HostScene& s, const float* data, int w, int h, int channel
     if (w < 0 || h < 0) return fail(err, "negative image size");
     if (data && w > 0 && h > 0 && channels < 3) return fail(err, "environment maps need >= 3 channels");
     HostTexture t; t.kind = TEX_ENV; t.w = w; t.h = h; t.ch = channels;
-    if (data && w > 0 && h > 0) t.f32.assign(data, data + (size_t)w * h * channels);
+    if (data && w > 0 && h > 0 && !try_pack_rgbe(data, w, h, channels, t.rgbe))   // lossless 4 B/texel form, else the floats
+        t.f32.assign(data, data + (size_t)w * h * channels);
     s.textures.push_back(std::move(t)); return (int)s.textures.size() - 1;
 }
 int b_add_material(HostScene& s, const hrt_material* m, std::string& err)

@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <atomic>
 #include <cstring>
 #include <limits>
 #include <map>
@@ -337,28 +338,42 @@ void build_fast_bvh(const std::vector<float>& bmin, const std::vector<float>& bm
 // Exact repack of a decoded Radiance image (texture.cpp:99-115 -> stb_image stbi__hdr_convert: byte * 2^(e-136))
 // into one 32-bit word per texel; refuses (returns false) unless every texel round-trips bit for bit.
 // ------------------------------------------------------------------------------------------------------------
-bool try_pack_rgbe(const std::vector<float>& f32, int w, int h, int ch, std::vector<uint32_t>& rgbe)
+bool try_pack_rgbe(const float* f32, int w, int h, int ch, std::vector<uint32_t>& rgbe)
 {
-    if (ch < 3 || w <= 0 || h <= 0) return false;
-    size_t n = (size_t)w * h;
+    if (!f32 || ch < 3 || w <= 0 || h <= 0) return false;
+    const size_t n = (size_t)w * h;
     rgbe.resize(n);
-    for (size_t i = 0; i < n; ++i) {
-        const float* p = &f32[i * ch];
-        float m = std::max(p[0], std::max(p[1], p[2]));
-        if (!(p[0] >= 0) || !(p[1] >= 0) || !(p[2] >= 0) || !std::isfinite(m)) { rgbe.clear(); return false; }
-        if (m == 0) { rgbe[i] = 0; continue; }
-        int ex; std::frexp(m, &ex);
-        int e = ex + 128;
-        if (e < 1 || e > 255) { rgbe.clear(); return false; }
-        float f = std::ldexp(1.0f, e - 136);
-        uint32_t word = (uint32_t)e << 24;
-        for (int c = 0; c < 3; ++c) {
-            float q = p[c] / f;
-            if (!(q >= 0 && q <= 255) || q != std::floor(q) || (float)(int)q * f != p[c]) { rgbe.clear(); return false; }
-            word |= (uint32_t)(int)q << (8 * c);
+    std::atomic<bool> ok{true};
+    // Integer form of "p == q * 2^(e-136) with q an integer in [0,255]": with mexp the biased exponent of the largest
+    // channel, e = mexp + 2 (= frexp exponent + 128) and a channel 1.mant * 2^(cexp-127) is q = 1.mant * 2^(cexp-mexp+7).
+    auto work = [&](size_t i0, size_t i1) {
+        for (size_t i = i0; i < i1; ++i) {
+            if ((i & 4095u) == 0 && !ok.load(std::memory_order_relaxed)) return;
+            uint32_t b[3]; std::memcpy(b, f32 + i * (size_t)ch, 12);
+            const uint32_t m = std::max(b[0], std::max(b[1], b[2]));
+            if ((b[0] | b[1] | b[2]) & 0x80000000u) { ok = false; return; }     // negative (or -0): keep the float array
+            if (m == 0) { rgbe[i] = 0; continue; }
+            const int mexp = (int)(m >> 23);
+            if (mexp < 8 || mexp > 253) { ok = false; return; }                 // denormal / tiny / inf / NaN
+            uint32_t word = (uint32_t)(mexp + 2) << 24;
+            for (int c = 0; c < 3; ++c) {
+                if (b[c] == 0) continue;
+                const int s = (int)(b[c] >> 23) - mexp + 7;                     // q = 1.mant * 2^s, s <= 7
+                if (s < 0) { ok = false; return; }
+                const uint32_t mant = (b[c] & 0x7fffffu) | 0x800000u;
+                if (mant & ((1u << (23 - s)) - 1u)) { ok = false; return; }     // q is not an integer
+                word |= (mant >> (23 - s)) << (8 * c);
+            }
+            rgbe[i] = word;
         }
-        rgbe[i] = word;
-    }
+    };
+    int nt = (int)std::thread::hardware_concurrency(); if (nt < 1) nt = 1; if (nt > 16) nt = 16;
+    if (n < (1u << 16)) nt = 1;
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; ++t) th.emplace_back(work, n * (size_t)t / (size_t)nt, n * (size_t)(t + 1) / (size_t)nt);
+    work(0, n / (size_t)nt);
+    for (auto& t : th) t.join();
+    if (!ok) { rgbe.clear(); rgbe.shrink_to_fit(); return false; }
     return true;
 }
 

@@ -16,8 +16,7 @@ struct HostTexture {
     int w = 0, h = 0, ch = 0;
     std::vector<uint8_t> u8;
     std::vector<float> f32;
-    std::vector<uint32_t> rgbe;     // filled at commit when every texel of an env map is exactly RGBE-representable
-    int rgbe_tried = 0;
+    std::vector<uint32_t> rgbe;     // env maps whose every texel is exactly RGBE-representable are kept ONLY in this form (f32 stays empty)
 };
 
 struct RefBvh {                      // bvh.cpp:6-61 in index form
@@ -90,7 +89,7 @@ std::string flatten(HostScene& s, int bvh_mode, uint64_t seed);
 
 // Exact-repack test for environment maps: true (and rgbe filled) when every texel equals ldexp(m, e - 136) with
 // 8-bit mantissas and one shared exponent, which is what stb_image produces for Radiance .hdr files (texture.cpp:99-115).
-bool try_pack_rgbe(const std::vector<float>& f32, int w, int h, int ch, std::vector<uint32_t>& rgbe);
+bool try_pack_rgbe(const float* f32, int w, int h, int ch, std::vector<uint32_t>& rgbe);
 
 // Camera ctor camera.h:9-30
 DCamera make_camera(const hrt_camera& c);

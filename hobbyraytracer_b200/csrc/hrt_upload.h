@@ -34,10 +34,9 @@ DScene make_dscene(HostScene& s, Up& up)
         x.kind = t.kind; x.rgb[0] = t.rgb[0]; x.rgb[1] = t.rgb[1]; x.rgb[2] = t.rgb[2];
         x.even = t.even; x.odd = t.odd; x.w = t.w; x.h = t.h; x.ch = t.ch; x.data = nullptr;
         if (t.kind == TEX_IMAGE && !t.u8.empty()) x.data = up.put(t.u8.data(), t.u8.size());
-        if (t.kind == TEX_ENV && !t.f32.empty()) {
-            if (t.rgbe.empty() && t.rgbe_tried == 0) { t.rgbe_tried = 1; try_pack_rgbe(t.f32, t.w, t.h, t.ch, t.rgbe); }
+        if (t.kind == TEX_ENV) {
             if (!t.rgbe.empty()) { x.kind = TEX_ENV_RGBE; x.data = up.put(t.rgbe.data(), t.rgbe.size() * sizeof(uint32_t)); }
-            else x.data = up.put(t.f32.data(), t.f32.size() * sizeof(float));
+            else if (!t.f32.empty()) x.data = up.put(t.f32.data(), t.f32.size() * sizeof(float));
         }
         tex[i] = x;
     }

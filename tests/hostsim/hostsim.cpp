@@ -95,6 +95,17 @@ int hsim_trace_batch(hsim_scene* s, const float* rays, int64_t n, uint32_t* prim
     s->cnt.nodes = nodes; s->cnt.prims = prims; s->cnt.fallbacks = fb; s->cnt.amb = amb; s->cnt.bad = bad;
     return 0;
 }
+// Texture::colourValue through the device header on the flattened scene (exercises the lossless RGBE repack of env maps)
+int hsim_texture_eval(hsim_scene* s, int tex, const float* in, int64_t n, float* out)
+{
+    if (!s->host.committed || tex < 0 || tex >= s->d.n_textures) { g_err = "bad texture / scene not committed"; return HRT_ERR_ARG; }
+    for (int64_t i = 0; i < n; ++i) {
+        V3 c = tex_value(s->d, tex, in[i*5], in[i*5+1], v3(in[i*5+2], in[i*5+3], in[i*5+4]));
+        out[i*3] = c.x; out[i*3+1] = c.y; out[i*3+2] = c.z;
+    }
+    return 0;
+}
+int hsim_texture_kind(hsim_scene* s, int tex) { return (s->host.committed && tex >= 0 && tex < s->d.n_textures) ? s->d.textures[tex].kind : -1; }
 int hsim_counters(hsim_scene* s, uint64_t* out3) { out3[0] = s->cnt.nodes; out3[1] = s->cnt.prims; out3[2] = s->cnt.fallbacks; return 0; }
 int hsim_counters5(hsim_scene* s, uint64_t* out5) { out5[0] = s->cnt.nodes; out5[1] = s->cnt.prims; out5[2] = s->cnt.fallbacks; out5[3] = s->cnt.amb; out5[4] = s->cnt.bad; return 0; }
 

@@ -252,3 +252,26 @@ def test_nan_rays(orc, hsim, mode):
         ro, rh = o.trace(rays, rng_seed=3, extras=False), h.trace(rays, rng_seed=3, extras=False)
         assert np.array_equal(ro["prim"], rh["prim"]) and np.array_equal(bits(ro["t"]), bits(rh["t"]))
         assert (ro["prim"][:32] != abi.MISS).all()
+
+
+def test_env_map_rgbe_repack_is_lossless(orc, hsim):
+    """Decoded Radiance images are stored as one RGBE word per texel on the device (hrt_host.cpp try_pack_rgbe): lookups
+    must equal the float lookups of texture.cpp:76-97 bit for bit; anything not exactly representable keeps its floats."""
+    hsim._sig("texture_kind", abi.C.c_int, [abi.C.c_void_p, abi.C.c_int])
+    rng = np.random.default_rng(3)
+    rgbe = rng.integers(0, 256, (64, 128, 4), dtype=np.uint8)
+    rgbe[..., 3] = rng.integers(100, 160, (64, 128))            # exponents around 1.0
+    rgbe[0, :8] = 0                                             # black texels (e = 0)
+    rgbe[1, :8, :3] = [[255, 0, 1]] * 8                         # un-normalised mantissas decode and repack too
+    exact = scenes.rgbe_to_float(rgbe)
+    inexact = exact.copy(); inexact[5, 7, 1] = np.float32(0.1)  # 0.1 has no 8-bit mantissa
+    negative = exact.copy(); negative[9, 3, 0] = -1.0
+    uvp = rng.random((5000, 5)).astype(np.float32) * 1.2 - 0.1
+    for data, packed in ((exact, True), (inexact, False), (negative, False)):
+        sd = abi.SceneDesc()
+        t = sd.env(data)
+        sd.background = t
+        sd.add(sd.sphere((0, 0, 0), 1, sd.material(abi.MAT_LAMBERTIAN)))
+        o, h = sd.build(orc), sd.build(hsim)
+        assert (hsim.fn("texture_kind")(h.h, t) == 4) == packed
+        assert np.array_equal(bits(o.texture_eval(t, uvp)), bits(h.texture_eval(t, uvp)))

@@ -31,6 +31,9 @@ constexpr float SHEAR_LIMIT = 64.0f;         // max|d| / |d[kZ]| above which ITr
 constexpr float SLAB_WIDEN = 4.76837158e-7f; // 2^-21: widening of the SAH-node slab interval (conservative vs aabb.h)
 constexpr int HIT_RESOLVED = 2;              // Hit::flags: answer came from pass 2 + replay
 constexpr int HIT_FALLBACK = 4;              // Hit::flags: answer came from trace_ref (last resort)
+#ifndef HRT_KZ_MODE
+#define HRT_KZ_MODE 0     // 0: one mesh walk per kZ value (compile-time permutation), 1: run-time permutation, 2: run-time only for warps that disagree
+#endif
 constexpr int KMAX = 16;                     // candidates a replay can hold
 
 struct TraceCounters { unsigned long long nodes, prims, fallbacks, amb, bad; };
@@ -77,6 +80,7 @@ HRT_HD void slab2(const float4& n0, const float4& n1, const float4& n2, V3 o, V3
     tn1 -= fabsf(tn1) * SLAB_WIDEN; tf1 += fabsf(tf1) * SLAB_WIDEN;
 }
 
+HRT_HD bool recip_ok(V3 id) { return hrt_finite(id.x) && hrt_finite(id.y) && hrt_finite(id.z); }   // id = 1/d computed by the caller
 HRT_HD bool dir_ok(V3 d)                    // every component non-zero with a finite reciprocal
 {
     return hrt_finite(1.0f / d.x) && hrt_finite(1.0f / d.y) && hrt_finite(1.0f / d.z);
@@ -85,16 +89,20 @@ HRT_HD bool dir_ok(V3 d)                    // every component non-zero with a f
 // ---- ITriangle::hit with the per-ray part hoisted -------------------------------------------------------------------
 // triangle.cpp:70-84 depend on the ray only: the permutation (kZ from the ORIGIN) and the shear constants.  KZ is a
 // template parameter so that the permutation costs no selects; the arithmetic per triangle is itriangle()'s, verbatim.
-struct TriRay { V3 o; float sX, sY, sZ; };
+struct TriRay { V3 o; float sX, sY, sZ; int kz; };
 
-template <int KZ> HRT_HD V3 permute(V3 v)
+// KZ = 0, 1, 2: compile-time permutation (no selects).  KZ = 3: the permutation is taken from q.kz at run time (two
+// selects per component) so that a warp whose rays disagree on kZ — secondary rays, whose origins lie all over the
+// mesh — walks the tree once instead of once per kZ value.  The arithmetic on the permuted components is the same.
+template <int KZ> HRT_HD V3 permute(V3 v, int kz)
 {
+    if (KZ == 3) return kz == 0 ? v3(v.y, v.z, v.x) : (kz == 1 ? v3(v.z, v.x, v.y) : v);
     return KZ == 0 ? v3(v.y, v.z, v.x) : (KZ == 1 ? v3(v.z, v.x, v.y) : v);   // (kX, kY, kZ) = (KZ+1, KZ+2, KZ) mod 3
 }
-template <int KZ> HRT_HD TriRay tri_ray(const Ray& r)
+template <int KZ> HRT_HD TriRay tri_ray(const Ray& r, int kz)
 {
-    V3 d = permute<KZ>(r.d);
-    TriRay q; q.o = r.o;
+    V3 d = permute<KZ>(r.d, kz);
+    TriRay q; q.o = r.o; q.kz = kz;
     q.sX = -d.x / d.z; q.sY = -d.y / d.z; q.sZ = 1.0f / d.z;
     return q;
 }
@@ -103,7 +111,7 @@ HRT_HD int tri_kz(V3 o) { return o.x > o.z ? (o.x > o.y ? 0 : 1) : 2; }        /
 template <int KZ>
 HRT_HD bool itriangle_t(const float4& P0, const float4& P1, const float4& P2, const TriRay& q, float t_max, float& t)
 {
-    V3 p0t = permute<KZ>(xyz(P0) - q.o), p1t = permute<KZ>(xyz(P1) - q.o), p2t = permute<KZ>(xyz(P2) - q.o);
+    V3 p0t = permute<KZ>(xyz(P0) - q.o, q.kz), p1t = permute<KZ>(xyz(P1) - q.o, q.kz), p2t = permute<KZ>(xyz(P2) - q.o, q.kz);
     p0t.x += q.sX * p0t.z; p0t.y += q.sY * p0t.z;
     p1t.x += q.sX * p1t.z; p1t.y += q.sY * p1t.z;
     p2t.x += q.sX * p2t.z; p2t.y += q.sY * p2t.z;
@@ -129,10 +137,9 @@ HRT_HD bool itriangle_t(const float4& P0, const float4& P1, const float4& P2, co
 // evaluated for a triangle that was accepted — it decides whether the reference could have reached the triangle at
 // this bound and yields entry_i.
 template <int KZ, bool COLLECT, bool COUNT>
-HRT_HDN inline void mesh_walk(const DMesh& m, const Ray& lr, float t_min, Best& b, Collector& k, int obj, TraceCounters* cnt)
+HRT_HDN inline void mesh_walk(const DMesh& m, const Ray& lr, const V3 id, int kz, float t_min, Best& b, Collector& k, int obj, TraceCounters* cnt)
 {
-    const V3 id = v3(1.0f / lr.d.x, 1.0f / lr.d.y, 1.0f / lr.d.z);
-    const TriRay q = tri_ray<KZ>(lr);
+    const TriRay q = tri_ray<KZ>(lr, kz);
     const float t_lo = fminf(t_min, 0.0f);           // ITriangle::hit ignores t_min but only reports t > 0
     int stack[FAST_MAX_DEPTH + 4]; int sp = 0;
     int node = m.fast_root;
@@ -191,16 +198,21 @@ HRT_HD bool shear_ok(const Ray& lr, int kZ)
 }
 
 template <bool COLLECT, bool COUNT>
-HRT_HDN inline void object_walk(const DScene& s, int i, const Ray& r, float t_min, Best& b, Collector& k, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
+HRT_HDN inline void object_walk(const DScene& s, int i, const Ray& r, const V3 rid, float t_min, Best& b, Collector& k, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
 {
     const DObject& ob = s.objects[i];
     if (ob.kind == SHAPE_MESH && !ob.medium) {
         const DMesh& m = s.meshes[ob.mesh];
         if (m.ref_root < 0) return;
-        Ray lr = to_local(s, ob, r);
-        if (!dir_ok(lr.d) || !(hrt_finite(lr.o.x) && hrt_finite(lr.o.y) && hrt_finite(lr.o.z))) { b.bad = 1; return; }
+        // the three IEEE reciprocals of a ray are computed once per coordinate frame (they were 6 % of the kernel's
+        // instructions when every walk level recomputed them, profiles/ r1c): an unwrapped mesh shares the world ray's
+        Ray lr = r; V3 id = rid;
+        if (ob.xf_count > 0) {
+            lr = to_local(s, ob, r);
+            id = v3(1.0f / lr.d.x, 1.0f / lr.d.y, 1.0f / lr.d.z);
+            if (!recip_ok(id) || !(hrt_finite(lr.o.x) && hrt_finite(lr.o.y) && hrt_finite(lr.o.z))) { b.bad = 1; return; }
+        }
         if (m.fast_root >= 0) {          // whole-mesh rejection before any per-ray triangle set-up: most camera rays miss the mesh
-            const V3 id = v3(1.0f / lr.d.x, 1.0f / lr.d.y, 1.0f / lr.d.z);
             const float4* N = m.fast_nodes + 4 * (size_t)m.fast_root;
             float tn0, tf0, tn1, tf1;
             slab2(HRT_LD4(N), HRT_LD4(N + 1), HRT_LD4(N + 2), lr.o, id, tn0, tf0, tn1, tf1);
@@ -209,11 +221,21 @@ HRT_HDN inline void object_walk(const DScene& s, int i, const Ray& r, float t_mi
         }
         const int kZ = tri_kz(lr.o);
         if (!COLLECT && !shear_ok(lr, kZ)) { b.shear = 1; return; }             // pass 2 will collect every hit along this ray
-        switch (kZ) {
-        case 0: mesh_walk<0, COLLECT, COUNT>(m, lr, t_min, b, k, i, cnt); break;
-        case 1: mesh_walk<1, COLLECT, COUNT>(m, lr, t_min, b, k, i, cnt); break;
-        default: mesh_walk<2, COLLECT, COUNT>(m, lr, t_min, b, k, i, cnt); break;
+#if HRT_KZ_MODE == 1
+        mesh_walk<3, COLLECT, COUNT>(m, lr, id, kZ, t_min, b, k, i, cnt);
+#else
+#if HRT_KZ_MODE == 2 && defined(__CUDA_ARCH__)
+        if (!__all_sync(__activemask(), kZ == __shfl_sync(__activemask(), kZ, __ffs(__activemask()) - 1))) {
+            mesh_walk<3, COLLECT, COUNT>(m, lr, id, kZ, t_min, b, k, i, cnt);
+            return;
         }
+#endif
+        switch (kZ) {
+        case 0: mesh_walk<0, COLLECT, COUNT>(m, lr, id, 0, t_min, b, k, i, cnt); break;
+        case 1: mesh_walk<1, COLLECT, COUNT>(m, lr, id, 1, t_min, b, k, i, cnt); break;
+        default: mesh_walk<2, COLLECT, COUNT>(m, lr, id, 2, t_min, b, k, i, cnt); break;
+        }
+#endif
         return;
     }
     float t; uint32_t prim;
@@ -225,9 +247,8 @@ HRT_HDN inline void object_walk(const DScene& s, int i, const Ray& r, float t_mi
 
 // ---- top level: SAH tree over world-list entries ----------------------------------------------------------------------------
 template <bool COLLECT, bool COUNT>
-HRT_HDN inline void world_walk(const DScene& s, const Ray& r, float t_min, Best& b, Collector& k, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
+HRT_HDN inline void world_walk(const DScene& s, const Ray& r, const V3 id, float t_min, Best& b, Collector& k, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
 {
-    const V3 id = v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
     // RotateQuat objects report t in units of their normalised direction (rotateQuat.cpp:51):
     // reported t >= world t * |d| * tlas_cull_scale, so entry distances are scaled down before they cull.
     const float cull = s.tlas_cull_scale > 0.0f ? fminf(1.0f, length(r.d) * s.tlas_cull_scale) * 0.9999f : 1.0f;
@@ -253,7 +274,7 @@ HRT_HDN inline void world_walk(const DScene& s, const Ray& r, float t_min, Best&
             if (h0) { node = c0; continue; }
             if (h1) { node = c1; continue; }
         } else {
-            object_walk<COLLECT, COUNT>(s, ~node, r, t_min, b, k, key, bounce, cnt);
+            object_walk<COLLECT, COUNT>(s, ~node, r, id, t_min, b, k, key, bounce, cnt);
         }
         if (sp == 0 || b.bad) break;
         node = stack[--sp];
@@ -325,7 +346,7 @@ HRT_COLD Hit trace_resolve(const DScene& s, const Ray& r, float t_min, float t_m
         Best b; b.t = 0.0f; b.a = 0.0f; b.prim = HRT_MISS; b.obj = -1; b.amb = 0; b.bad = 0; b.shear = 0; b.t_max = t_max;
         Collector k; k.n = 0; k.overflow = 0; k.bad = 0;
         k.beta = shear ? t_max : beta;
-        world_walk<true, COUNT>(s, r, t_min, b, k, key, bounce, cnt);
+        world_walk<true, COUNT>(s, r, v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z), t_min, b, k, key, bounce, cnt);
         if (!k.overflow && !k.bad && !b.bad && replay(s, r, t_min, t_max, k, key, bounce, h)) { h.flags |= HIT_RESOLVED; return h; }
     }
     if (COUNT) { cnt->fallbacks += 1; cnt->bad += 1; }
@@ -347,11 +368,12 @@ HRT_HD Hit trace_fast(const DScene& s, const Ray& r, float t_min, float t_max, c
         if (s.nan_obj >= 0) { h.t = int_as_float(0x7fc00000); h.prim = s.nan_prim; h.obj = s.nan_obj; }
         return h;
     }
-    const bool ok = dir_ok(r.d) && hrt_finite(r.o.x) && hrt_finite(r.o.y) && hrt_finite(r.o.z);
+    const V3 id = v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
+    const bool ok = recip_ok(id) && hrt_finite(r.o.x) && hrt_finite(r.o.y) && hrt_finite(r.o.z);
     Best b; b.t = 0.0f; b.a = 0.0f; b.prim = HRT_MISS; b.obj = -1; b.amb = 0; b.bad = ok ? 0 : 1; b.shear = 0; b.t_max = t_max;
     if (ok) {
         Collector* none = nullptr;
-        world_walk<false, COUNT>(s, r, t_min, b, *none, key, bounce, cnt);       // pass 1 never touches the collector
+        world_walk<false, COUNT>(s, r, id, t_min, b, *none, key, bounce, cnt);       // pass 1 never touches the collector
         if (!b.bad && !b.amb && !b.shear) { h.t = b.prim == HRT_MISS ? 0.0f : b.t; h.prim = b.prim; h.obj = b.obj; return h; }
     }
     return trace_resolve<COUNT>(s, r, t_min, t_max, key, bounce, cnt, b.bad, b.shear, cull_bound(b));

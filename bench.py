@@ -181,7 +181,7 @@ def run_own(args):
     fsum = torch.zeros(npix * 3, dtype=torch.float32, device="cuda")
     rgb8 = torch.zeros(npix * 3, dtype=torch.uint8, device="cuda")
     stream = torch.cuda.current_stream().cuda_stream
-    flags = abi.RENDER_MEGAKERNEL if args.megakernel else 0
+    flags = abi.RENDER_MEGAKERNEL if args.megakernel else (abi.RENDER_WAVEFRONT_V1 if args.pipeline == "v1" else 0)
 
     def step():
         film.zero_()
@@ -259,7 +259,7 @@ def run_own(args):
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "samples_per_s": paths / (ms * 1e-3), "samples_per_s_per_gpu": paths / (ms * 1e-3) / world, "rays_per_sample": rays / max(paths, 1),
                 "config": {"workload": f"{info['name']} {w}x{h}, {spp} spp split over {world} GPU(s)", "width": w, "height": h, "spp": spp, "max_depth": 50,
-                           "bvh": args.bvh, "n_prims": n_prims, "pipeline": "megakernel" if args.megakernel else "persistent wavefront",
+                           "bvh": args.bvh, "n_prims": n_prims, "pipeline": "megakernel" if args.megakernel else ("persistent wavefront, every ray queued" if args.pipeline == "v1" else "wavefront, camera paths fused into the trace pass"),
                            "cache": "the wavefront queues (4 Mi entries: rays + hits + path state = 600 MB) exceed the 126 MB L2 and are rewritten every pass; no flush needed"},
                 "e2e": {"value": float(e2e_r.item()) / float(e2e_s.item()) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": scene_bytes,
                         "d2h_bytes_per_step": npix * 15, "steps": e2e_steps, "includes": "scene build + BVH build + upload, render, float film + 8-bit image read-back"},
@@ -293,6 +293,7 @@ def main():
     ap.add_argument("--quads", type=int, default=2290)
     ap.add_argument("--bvh", default="sah", choices=["sah", "reference"])
     ap.add_argument("--megakernel", action="store_true")
+    ap.add_argument("--pipeline", default="fused", choices=["fused", "v1"], help="fused: camera paths traced in the trace pass, only hits are queued; v1: every ray queued")
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)

@@ -21,6 +21,7 @@ MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_ISOTROPIC, MAT_DIFFUSE_LIGHT, MAT
 XF_TRANSLATE, XF_SCALE, XF_ROTATE_QUAT, XF_ROTATE_Y, XF_ROTATE_EULER_DEG, XF_ROTATE_Y_DEG = range(6)
 BVH_REFERENCE, BVH_SAH, BVH_LBVH_GPU = range(3)
 RENDER_MEGAKERNEL = 1
+RENDER_WAVEFRONT_V1 = 2
 
 
 class Material(C.Structure):

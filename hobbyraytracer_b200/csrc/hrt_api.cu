@@ -64,6 +64,7 @@ struct hrt_scene {
     float4* tb_rays = nullptr; Hit* tb_hits = nullptr;
     uint32_t* tb_prim = nullptr; float* tb_t = nullptr; long long tb_capacity = 0;
     hrt_stats stats{};
+    bool last_secondary_heavy = false;
 };
 
 namespace {
@@ -142,9 +143,11 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
     const int first = p->sample_first, count = p->sample_count > 0 ? p->sample_count : p->spp;
     const int max_depth = p->max_depth > 0 ? p->max_depth : 50;
     const bool mega = (p->flags & HRT_RENDER_MEGAKERNEL) != 0;
+    const bool v1 = (p->flags & HRT_RENDER_WAVEFRONT_V1) != 0;       // queue-everything wavefront with regeneration (kept for A/B)
     const unsigned long long total = (unsigned long long)npix * (unsigned long long)count;
     unsigned long long cap = wave_capacity();
     if (cap > total) cap = (total + 1023ull) / 1024ull * 1024ull;
+    if (!v1 && cap < (1ull << 18)) cap = 1ull << 18;                      // the fused-primary trace pass keeps an append margin (hrt_kernels.cu)
     if (mega) cap = 1024;
     int rc = ensure_job(s, (unsigned int)cap); if (rc < 0) return rc;
     WaveJob j = s->job;
@@ -160,15 +163,16 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
     while (s->events.size() < (size_t)(EV_PER_CHUNK * CTL_RING + 2)) { cudaEvent_t e; CK(cudaEventCreate(&e)); s->events.push_back(e); }
     cudaEvent_t ev_begin = s->events[EV_PER_CHUNK * CTL_RING], ev_end = s->events[EV_PER_CHUNK * CTL_RING + 1];
 
-    WaveCtl init{}; init.total_paths = total;
+    WaveCtl init{}; init.total_paths = (mega || v1) ? total : wave2_total_claims(j);
     CK(cudaMemcpyAsync(j.ctl, &init, sizeof(init), cudaMemcpyHostToDevice, st));
     CK(cudaEventRecord(ev_begin, st));
     s->stats.paths += total;
     if (mega) {
         launch_render_mega(s->d, j, dc, s->sm_count, st, &s->stats.launches);
     } else {
-        launch_wave_init(j, dc, s->sm_count, st, &s->stats.launches);
+        if (v1) launch_wave_init(j, dc, s->sm_count, st, &s->stats.launches);
         int it = 0, issued = 0, retired = 0; bool done = false;
+        bool secondary_heavy = s->last_secondary_heavy;      // start from what the previous render of this scene found
         auto retire = [&](int chunk) -> int {               // waits for the chunk, adds its kernel times, looks at its snapshot
             cudaEvent_t* ev = s->events.data() + (size_t)EV_PER_CHUNK * (size_t)(chunk % CTL_RING);
             CK(cudaEventSynchronize(ev[2 * CHUNK + 1]));
@@ -180,7 +184,12 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
             const WaveCtl& c = s->h_ctl[chunk % CTL_RING];
             const int o = (chunk * CHUNK + CHUNK) & 1;       // queue the last shade pass of the chunk filled
             const unsigned long long handed = c.next_path < c.total_paths ? c.next_path : c.total_paths;
-            if (c.n_front[o] == 0 && handed == c.base[o] && handed == c.total_paths) done = true;
+            if (!v1 && c.next_path > 0) {                    // fused-primary: secondary rays per camera path so far (claims are CLAIM paths)
+                const double paths = (double)handed * (double)total / (double)(c.total_paths ? c.total_paths : 1);
+                secondary_heavy = (double)c.rays > 0.75 * paths;
+                s->last_secondary_heavy = secondary_heavy;
+            }
+            if (v1 ? (c.n_front[o] == 0 && handed == c.base[o] && handed == c.total_paths) : (c.n_front[o] == 0 && handed == c.total_paths)) done = true;
             return 0;
         };
         while (!done) {
@@ -188,9 +197,11 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
             cudaEvent_t* ev = s->events.data() + (size_t)EV_PER_CHUNK * (size_t)(issued % CTL_RING);
             for (int k = 0; k < CHUNK; ++k, ++it) {
                 CK(cudaEventRecord(ev[2 * k], st));
-                launch_wave_trace(s->d, j, it, s->sm_count, st, &s->stats.launches);
+                if (v1) launch_wave_trace(s->d, j, it, s->sm_count, st, &s->stats.launches);
+                else launch_wave2_trace(s->d, j, dc, it, secondary_heavy, s->sm_count, st, &s->stats.launches);
                 CK(cudaEventRecord(ev[2 * k + 1], st));
-                launch_wave_shade(s->d, j, dc, it, s->sm_count, st, &s->stats.launches);
+                if (v1) launch_wave_shade(s->d, j, dc, it, s->sm_count, st, &s->stats.launches);
+                else launch_wave2_shade(s->d, j, it, s->sm_count, st, &s->stats.launches);
             }
             CK(cudaEventRecord(ev[2 * CHUNK], st));
             CK(cudaMemcpyAsync(&s->h_ctl[issued % CTL_RING], j.ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, st));
@@ -208,7 +219,8 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
     fin = s->h_ctl[0];
     float ms = 0; CK(cudaEventElapsedTime(&ms, ev_begin, ev_end));
     s->stats.ms_total += ms;
-    s->stats.rays += fin.rays; s->stats.retraced += fin.resolved; s->stats.prim_tests += fin.fallbacks;
+    s->stats.rays += fin.rays + ((mega || v1) ? 0ull : total);       // fused-primary: the control block counts the secondary rays only
+    s->stats.retraced += fin.resolved; s->stats.prim_tests += fin.fallbacks;
     if (fin.fallbacks && getenv("HRT_DEBUG_FALLBACK"))
         for (unsigned long long k = 0; k < fin.fallbacks && k < 16; ++k) {
             const float* g = fin.dbg[k]; unsigned int st; memcpy(&st, &g[7], 4); int pix; memcpy(&pix, &g[3], 4);

@@ -249,6 +249,196 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave_shade(DScene s, WaveJob j,
     }
 }
 
+// ---- fused-primary wavefront (the default pipeline) ---------------------------------------------------------------------------
+// profiles/ r1c: on shiny_teapot 90 % of all rays are camera rays and 85 % of those leave the scene at once, yet every
+// one of them was written to a queue (64 B), read back twice, given a 16 B hit record and shaded by a second kernel whose
+// time went to waiting for those streams (k_wave_shade: 3.3 TB/s of DRAM traffic, issue slots 42 % busy).  Here a camera
+// path never touches a queue unless it HITS something:
+//   k_wave2_trace, one persistent grid: (1) secondary rays of queue q -> hits[]; (2) every warp then claims CLAIM camera
+//       paths at a time from the global counter, generates them (K1), traces them (K2) and
+//         miss -> background lookup + film add on the spot (K4/K5: the path is finished),
+//         hit  -> appended behind the secondary entries (warp ballot + one atomic per warp, K3) for the shade pass,
+//       until the image is out of paths or the queue is (conservatively) full;
+//   k_wave2_shade: shades the n_sec + n_prim entries, compacts the survivors to the front of queue q^1.
+// The film is integer, so the image is bit-identical to the other pipelines whatever the interleaving.
+// A claim is one warp-sized pixel unit (an 8x4 tile, or 32 consecutive pixels when the film is not whole tiles) times
+// CLAIM_SPP consecutive samples: the lane keeps its pixel, loops over the samples and sums the finished (missed) ones as
+// fixed-point integers in registers — integer sums associate, so one atomic per channel and claim leaves the same film
+// as one atomic per sample.  WaveCtl::next_path / total_paths count CLAIMS in this pipeline.
+#ifndef HRT_CLAIM_SPP
+#define HRT_CLAIM_SPP 4      // A/B on B200 (profiles/README.md r1d): 4 beats 2 and 8 on all four scenes
+#endif
+constexpr int CLAIM_SPP = HRT_CLAIM_SPP;
+constexpr int CLAIM = 32 * CLAIM_SPP;           // camera paths per claim (upper bound of what a warp appends after a room check)
+
+__device__ __forceinline__ unsigned int ld_relaxed(const unsigned int* p) { return *(const volatile unsigned int*)p; }
+__device__ __forceinline__ unsigned long long ld_relaxed(const unsigned long long* p) { return *(const volatile unsigned long long*)p; }
+
+__host__ __device__ inline unsigned int wave2_units(const WaveJob& j) { return j.tiles_x > 0 ? (unsigned int)(j.tiles_x * j.tiles_y) : ((unsigned int)j.npix + 31u) / 32u; }
+__host__ __device__ inline unsigned int wave2_sblocks(const WaveJob& j) { return ((unsigned int)j.s_count + CLAIM_SPP - 1u) / CLAIM_SPP; }
+
+struct FilmAcc { long long q[3]; unsigned long long flags; };
+__device__ __forceinline__ void acc_add(FilmAcc& a, V3 c)
+{
+    const float v[3] = {c.x, c.y, c.z};
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+        long long q; unsigned long long flag;
+        film_quantize(v[ch], ch, q, flag);
+        a.q[ch] += q; a.flags |= flag;
+    }
+}
+__device__ __forceinline__ void acc_flush(FilmAcc& a, long long* film, int pix)
+{
+    long long* px = film + (size_t)pix * FILM_LANES;
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) if (a.q[ch] != 0) { atomicAdd((unsigned long long*)(px + ch), (unsigned long long)a.q[ch]); a.q[ch] = 0; }
+    if (a.flags) { atomicOr((unsigned long long*)(px + 3), a.flags); a.flags = 0; }
+}
+
+// Two builds of the same kernel: 128 registers / 4 blocks per SM when camera paths dominate (shiny_teapot: +8 %), 64 registers /
+// 8 blocks per SM when incoherent secondary rays dominate (cornell, scattered balls, teapot_scene: +7-11 %; latency hiding
+// beats spilling there).  The host picks per chunk from the secondary-rays-per-camera-path ratio it reads in the control block.
+template <int MINB>
+__global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j, DCamera cam, int q)
+{
+    WaveCtl* c = j.ctl;
+    const unsigned int n_sec = c->n_front[q];
+    const unsigned long long total_claims = c->total_paths;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { c->rays += n_sec; c->n_front[q ^ 1] = 0; }   // nobody reads these in this kernel
+    const unsigned int lane = threadIdx.x & 31u;
+    const unsigned int warps_total = gridDim.x * (BLOCK / 32);
+    const unsigned int stride = warps_total * 32u;
+    const unsigned int room = j.capacity - n_sec;                                 // slots left for camera-path hits
+    const unsigned int margin = warps_total * (unsigned int)CLAIM;                // what the other warps may still append after a check
+    const unsigned int n_units = wave2_units(j);
+    float4* __restrict__ rays = j.rays[q];
+    unsigned int sec_i = (blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5)) * 32u + lane;
+    int c_left = 0, c_sl = 0, c_pix = -1, c_x = 0, c_y = 0;                         // the warp's claim: pixel of this lane, next sample, samples left
+    FilmAcc acc; acc.q[0] = acc.q[1] = acc.q[2] = 0; acc.flags = 0;
+    for (;;) {
+        Ray r; r.o = v3(0.0f); r.d = v3(0.0f);
+        unsigned int st = 0; int pix = 0; bool active, primary;
+        if (sec_i - lane < n_sec) {                                                 // warp-uniform: secondary entries first
+            primary = false; active = sec_i < n_sec;
+            if (active) {
+                float4 a = rays[2 * (size_t)sec_i], b = rays[2 * (size_t)sec_i + 1];
+                r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
+                pix = __float_as_int(a.w); st = __float_as_uint(b.w);
+            }
+        } else {
+            primary = true;
+            if (c_left == 0) {
+                if (c_pix >= 0) acc_flush(acc, j.film, c_pix);
+                unsigned long long k0 = 0;
+                if (lane == 0 && ld_relaxed(&c->n_prim[q]) + margin <= room && ld_relaxed(&c->next_path) < total_claims)
+                    k0 = atomicAdd(&c->next_path, 1ull) + 1ull;
+                k0 = __shfl_sync(0xffffffffu, k0, 0);
+                if (k0 == 0 || k0 - 1ull >= total_claims) break;
+                const unsigned int k = (unsigned int)(k0 - 1ull);
+                const unsigned int sb = k / n_units, unit = k - sb * n_units;        // claims of one sample block sweep the film
+                c_sl = (int)sb * CLAIM_SPP;
+                c_left = j.s_count - c_sl < CLAIM_SPP ? j.s_count - c_sl : CLAIM_SPP;
+                if (j.tiles_x > 0) {
+                    c_x = (int)(unit % (unsigned int)j.tiles_x) * 8 + (int)(lane & 7u);
+                    c_y = (int)(unit / (unsigned int)j.tiles_x) * 4 + (int)(lane >> 3);
+                    c_pix = c_y * j.width + c_x;
+                } else {
+                    const unsigned int pp = unit * 32u + lane;
+                    c_pix = pp < (unsigned int)j.npix ? (int)pp : -1;
+                    c_x = c_pix >= 0 ? c_pix % j.width : 0; c_y = c_pix >= 0 ? c_pix / j.width : 0;
+                }
+            }
+            active = c_pix >= 0;
+            pix = c_pix;
+            if (active) {
+                RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + c_sl), j.rng_mode);
+                r = primary_ray_xy(cam, j.width, j.height, c_x, j.height - c_y, key);
+                st = pack_state(c_sl, 0, false);
+            }
+            ++c_sl; --c_left;
+        }
+        Hit h; h.t = 0.0f; h.prim = HRT_MISS; h.obj = -1; h.flags = 0;
+        if (active) {
+            RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + (int)((st >> 8) & 0x7fffffu)), j.rng_mode);
+            h = s.fast ? trace_fast<false>(s, r, j.t_min, hrt_inf(), key, st & 0xffu, nullptr) : trace_ref(s, r, j.t_min, hrt_inf(), key, st & 0xffu);
+            if (h.flags & (HIT_RESOLVED | HIT_FALLBACK)) atomicAdd((h.flags & HIT_FALLBACK) ? &c->fallbacks : &c->resolved, 1ull);
+        }
+        if (!primary) {
+            if (active) j.hits[sec_i] = h;
+            sec_i += stride;
+            continue;
+        }
+        const bool hit = active && h.prim != HRT_MISS;
+        if (active && !hit) acc_add(acc, background_colour(s, r));                  // main.cpp:47-59: the path ends on the background
+        const unsigned int m_hit = __ballot_sync(0xffffffffu, hit);
+        if (m_hit) {
+            unsigned int e0 = 0;
+            if (lane == 0) e0 = atomicAdd(&c->n_prim[q], (unsigned int)__popc(m_hit));
+            e0 = __shfl_sync(0xffffffffu, e0, 0);
+            if (hit) {
+                const unsigned int e = n_sec + e0 + (unsigned int)__popc(m_hit & ((1u << lane) - 1u));
+                rays[2 * (size_t)e] = make_float4(r.o.x, r.o.y, r.o.z, __int_as_float(pix));
+                rays[2 * (size_t)e + 1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(st));
+                j.hits[e] = h;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(SHADE_BLOCK) k_wave2_shade(DScene s, WaveJob j, int q)
+{
+    __shared__ unsigned int w_go[SHADE_BLOCK / 32];
+    __shared__ unsigned int s_pos;
+    WaveCtl* c = j.ctl;
+    const int o = q ^ 1;
+    const unsigned int n = c->n_front[q] + c->n_prim[q];
+    if (blockIdx.x == 0 && threadIdx.x == 0) c->n_prim[o] = 0;                    // the next trace pass appends to queue o; nobody reads this here
+    const float4* __restrict__ rays = j.rays[q];
+    const unsigned int lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const unsigned int stride = gridDim.x * SHADE_BLOCK;
+    for (unsigned int base = blockIdx.x * SHADE_BLOCK; base < n; base += stride) {
+        const unsigned int i = base + threadIdx.x;
+        bool go = false; Ray r; V3 atten, result; int pix = 0; unsigned int st = 0; bool has_result = false;
+        r.o = v3(0.0f); r.d = v3(0.0f); atten = v3(1.0f); result = v3(0.0f);
+        if (i < n) {
+            float4 a = rays[2 * (size_t)i], b = rays[2 * (size_t)i + 1];
+            r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
+            pix = __float_as_int(a.w); st = __float_as_uint(b.w);
+            const Hit h = j.hits[i];
+            const unsigned int bounce = st & 0xffu; const int sl = (int)((st >> 8) & 0x7fffffu);
+            has_result = (st >> 31) != 0;
+            RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + sl), j.rng_mode);
+            if (bounce > 0) { float4 at4 = j.thr[q][i]; atten = v3(at4.x, at4.y, at4.z); }      // a camera path starts with attenuation 1 (main.cpp:40)
+            if (has_result) { float4 r4 = j.res[q][i]; result = v3(r4.x, r4.y, r4.z); }
+            V3 rad;
+            go = shade_segment(s, h, r, atten, rad, key, bounce);
+            if (rad.x != 0.0f || rad.y != 0.0f || rad.z != 0.0f) { result = result + rad; has_result = true; }
+            go = go && (int)bounce + 1 < j.max_depth;                               // MAX_DEPTH reached: the partial sum stands (main.cpp:43,78)
+            if (go) st = pack_state(sl, (int)bounce + 1, has_result);
+            else if (has_result) film_add(j.film, pix, result);                     // px += rayColour(...)  main.cpp:123
+        }
+        const unsigned int m_go = __ballot_sync(0xffffffffu, go);
+        if (lane == 0) w_go[warp] = (unsigned int)__popc(m_go);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned int t_go = 0;
+#pragma unroll
+            for (int w = 0; w < SHADE_BLOCK / 32; ++w) { unsigned int g = w_go[w]; w_go[w] = t_go; t_go += g; }
+            s_pos = t_go ? atomicAdd(&c->n_front[o], t_go) : 0u;
+        }
+        __syncthreads();
+        if (go) {
+            const unsigned int e2 = s_pos + w_go[warp] + (unsigned int)__popc(m_go & ((1u << lane) - 1u));
+            j.rays[o][2 * (size_t)e2] = make_float4(r.o.x, r.o.y, r.o.z, __int_as_float(pix));
+            j.rays[o][2 * (size_t)e2 + 1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(st));
+            j.thr[o][e2] = make_float4(atten.x, atten.y, atten.z, 0.0f);
+            if (has_result) j.res[o][e2] = make_float4(result.x, result.y, result.z, 0.0f);
+        }
+        __syncthreads();                                                            // the next pass of the loop rewrites the shared counters
+    }
+}
+
 // ---- megakernel ------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(BLOCK) k_render_mega(DScene s, WaveJob j, DCamera cam)
 {
@@ -313,6 +503,25 @@ void launch_wave_shade(const DScene& s, const WaveJob& j, const DCamera& cam, in
     long long want = ((long long)j.capacity + SHADE_BLOCK - 1) / SHADE_BLOCK, cap = (long long)sm_count * 8;
     k_wave_shade<<<(int)(want < cap ? want : cap), SHADE_BLOCK, 0, st>>>(s, j, cam, it & 1); *launches += 1;
     }
+}
+int wave2_trace_blocks(unsigned int capacity, int sm_count, int minb)
+{
+    long long cap = (long long)capacity / (4ll * CLAIM * (BLOCK / 32));            // keeps the append margin below 1/4 of the queue
+    long long want = (long long)sm_count * minb;                                    // one resident wave: the warps loop until the work is gone
+    if (cap < 1) cap = 1;
+    return (int)(want < cap ? want : cap);
+}
+unsigned long long wave2_total_claims(const WaveJob& j) { return (unsigned long long)wave2_units(j) * (unsigned long long)wave2_sblocks(j); }
+void launch_wave2_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, bool secondary_heavy, int sm_count, cudaStream_t st, uint64_t* launches)
+{
+    if (secondary_heavy) k_wave2_trace<8><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1);
+    else k_wave2_trace<4><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1);
+    *launches += 1;
+}
+void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches)
+{
+    long long want = ((long long)j.capacity + SHADE_BLOCK - 1) / SHADE_BLOCK, cap = (long long)sm_count * 8;
+    k_wave2_shade<<<(int)(want < cap ? want : cap), SHADE_BLOCK, 0, st>>>(s, j, it & 1); *launches += 1;
 }
 void launch_render_mega(const DScene& s, const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches)
 {

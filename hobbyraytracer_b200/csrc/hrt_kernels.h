@@ -20,7 +20,7 @@ struct WaveCtl {
     unsigned long long rays;            // closest-hit queries issued
     unsigned long long resolved;        // rays answered by pass 2 + replay (hrt_trace.cuh)
     unsigned long long fallbacks;       // rays answered by trace_ref
-    unsigned long long pad;
+    unsigned int n_prim[2];             // fused-primary pipeline: camera-path hits appended behind the n_front[q] secondary entries of queue q
     float dbg[16][8];                   // first rays that took the trace_ref fallback (o, pixel, d, state), for diagnosis
 };
 
@@ -56,6 +56,11 @@ void launch_eval_batch(const DScene& s, const float4* d_rays, const Hit* d_hits,
 void launch_wave_init(const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_wave_trace(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_wave_shade(const DScene& s, const WaveJob& j, const DCamera& cam, int it, int sm_count, cudaStream_t st, uint64_t* launches);
+// fused-primary wavefront (default): iteration `it` is trace2(secondary rays of queue it&1 + camera paths until the queue is full)
+// + shade2(queue it&1 -> survivors to queue (it+1)&1); no init pass, the control block starts zeroed with total_paths set
+unsigned long long wave2_total_claims(const WaveJob& j);   // value of WaveCtl::total_paths for this pipeline (it hands out claims, not paths)
+void launch_wave2_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, bool secondary_heavy, int sm_count, cudaStream_t st, uint64_t* launches);
+void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches);
 // one thread per path, whole rayColour loop (validation of the wavefront pipeline); same film
 void launch_render_mega(const DScene& s, const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches);
 

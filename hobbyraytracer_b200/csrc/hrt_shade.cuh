@@ -199,6 +199,15 @@ HRT_HD Ray primary_ray(const DCamera& c, int w, int h, int pidx, const RngKey& k
     return camera_ray(c, u, v);
 }
 
+// same ray from the pixel coordinates the caller already has (x = pIdx % W, y = H - pIdx / W, main.cpp:115-116)
+HRT_HD Ray primary_ray_xy(const DCamera& c, int w, int h, int x, int y, const RngKey& key)
+{
+    U4 j = rng_draw(key, BOUNCE_CAMERA, 0);
+    float u = ((float)x + linear_f(j.x, key.mode, 0.0f, 1.0f)) / (w - 1);
+    float v = ((float)y + linear_f(j.y, key.mode, 0.0f, 1.0f)) / (h - 1);
+    return camera_ray(c, u, v);
+}
+
 // ---- Film::tonemap + writeColour film.cpp:25-52 -----------------------------------------------------------------------------
 HRT_HD void tonemap_write(V3 c, uint8_t* px)
 {

@@ -31,9 +31,6 @@ constexpr float SHEAR_LIMIT = 64.0f;         // max|d| / |d[kZ]| above which ITr
 constexpr float SLAB_WIDEN = 4.76837158e-7f; // 2^-21: widening of the SAH-node slab interval (conservative vs aabb.h)
 constexpr int HIT_RESOLVED = 2;              // Hit::flags: answer came from pass 2 + replay
 constexpr int HIT_FALLBACK = 4;              // Hit::flags: answer came from trace_ref (last resort)
-#ifndef HRT_KZ_MODE
-#define HRT_KZ_MODE 0     // 0: one mesh walk per kZ value (compile-time permutation), 1: run-time permutation, 2: run-time only for warps that disagree
-#endif
 constexpr int KMAX = 16;                     // candidates a replay can hold
 
 struct TraceCounters { unsigned long long nodes, prims, fallbacks, amb, bad; };
@@ -130,66 +127,6 @@ HRT_HD bool itriangle_t(const float4& P0, const float4& P1, const float4& P2, co
     return true;
 }
 
-// ---- per-mesh SAH tree over the reference's bottom nodes ----------------------------------------------------------------
-// COLLECT = false: pass 1 (track the best candidate, cull by it).  COLLECT = true: pass 2 (fixed bound k.beta, every
-// candidate goes to the collector).  A leaf is one bottom node of the reference topology: its triangles are tested
-// first (exact ITriangle arithmetic); the reference's own slab test of the node box (six IEEE divisions) is only
-// evaluated for a triangle that was accepted — it decides whether the reference could have reached the triangle at
-// this bound and yields entry_i.
-template <int KZ, bool COLLECT, bool COUNT>
-HRT_HDN inline void mesh_walk(const DMesh& m, const Ray& lr, const V3 id, int kz, float t_min, Best& b, Collector& k, int obj, TraceCounters* cnt)
-{
-    const TriRay q = tri_ray<KZ>(lr, kz);
-    const float t_lo = fminf(t_min, 0.0f);           // ITriangle::hit ignores t_min but only reports t > 0
-    int stack[FAST_MAX_DEPTH + 4]; int sp = 0;
-    int node = m.fast_root;
-    for (;;) {
-        while (node >= 0) {
-            const float4* N = m.fast_nodes + 4 * (size_t)node;
-            float4 n0 = HRT_LD4(N), n1 = HRT_LD4(N + 1), n2 = HRT_LD4(N + 2), n3 = HRT_LD4(N + 3);
-            float tn0, tf0, tn1, tf1;
-            slab2(n0, n1, n2, lr.o, id, tn0, tf0, tn1, tf1);
-            if (COUNT) cnt->nodes += 2;
-            const float bound = COLLECT ? k.beta : cull_bound(b);
-            bool h0 = tn0 <= tf0 && tf0 >= t_lo && tn0 <= bound;
-            bool h1 = tn1 <= tf1 && tf1 >= t_lo && tn1 <= bound;
-            int c0 = float_as_int(n3.x), c1 = float_as_int(n3.y);
-            if (h0 && h1) {
-                if (tn1 < tn0) { int tmp = c0; c0 = c1; c1 = tmp; }
-                stack[sp++] = c1; node = c0;
-            } else if (h0) node = c0;
-            else if (h1) node = c1;
-            else { if (sp == 0) return; node = stack[--sp]; }
-        }
-        {
-            const uint32_t leaf = (uint32_t)(~node);
-            const float4* L = m.fast_leaves + 8 * (size_t)leaf;
-            const float4 a = HRT_LD4(L), c = HRT_LD4(L + 1);
-            const int triL = float_as_int(a.w), triR = float_as_int(c.w);
-            const float bound = COLLECT ? k.beta : cull_bound(b);
-            float tL = 0, tR = 0;
-            if (COUNT) cnt->prims += (triR != triL) ? 2 : 1;
-            bool hL = itriangle_t<KZ>(HRT_LD4(L + 2), HRT_LD4(L + 3), HRT_LD4(L + 4), q, bound, tL);
-            bool hR = triR != triL && itriangle_t<KZ>(HRT_LD4(L + 5), HRT_LD4(L + 6), HRT_LD4(L + 7), q, bound, tR);
-            if (hL || hR) {
-                float entry;
-                if (COUNT) cnt->nodes += 1;
-                if (hit_aabb_entry(xyz(a), xyz(c), lr, t_min, bound, entry)) {       // the reference's bottom node box, its arithmetic
-                    if (COLLECT) {
-                        if (hL) collect(k, tL, obj, m.prim_base + (uint32_t)triL, leaf * 2u);
-                        if (hR) collect(k, tR, obj, m.prim_base + (uint32_t)triR, leaf * 2u + 1u);
-                    } else {
-                        if (hL) consider(b, tL, fmaxf(entry, tL), m.prim_base + (uint32_t)triL, obj);
-                        if (hR) consider(b, tR, fmaxf(entry, tR), m.prim_base + (uint32_t)triR, obj);   // beyond the new bound: no effect
-                    }
-                }
-            }
-        }
-        if (sp == 0) return;
-        node = stack[--sp];
-    }
-}
-
 // shear conditioning of ITriangle for this (local) ray
 HRT_HD bool shear_ok(const Ray& lr, int kZ)
 {
@@ -197,70 +134,41 @@ HRT_HD bool shear_ok(const Ray& lr, int kZ)
     return dmax <= SHEAR_LIMIT * fabsf(comp(lr.d, kZ));
 }
 
-template <bool COLLECT, bool COUNT>
-HRT_HDN inline void object_walk(const DScene& s, int i, const Ray& r, const V3 rid, float t_min, Best& b, Collector& k, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
-{
-    const DObject& ob = s.objects[i];
-    if (ob.kind == SHAPE_MESH && !ob.medium) {
-        const DMesh& m = s.meshes[ob.mesh];
-        if (m.ref_root < 0) return;
-        // the three IEEE reciprocals of a ray are computed once per coordinate frame (they were 6 % of the kernel's
-        // instructions when every walk level recomputed them, profiles/ r1c): an unwrapped mesh shares the world ray's
-        Ray lr = r; V3 id = rid;
-        if (ob.xf_count > 0) {
-            lr = to_local(s, ob, r);
-            id = v3(1.0f / lr.d.x, 1.0f / lr.d.y, 1.0f / lr.d.z);
-            if (!recip_ok(id) || !(hrt_finite(lr.o.x) && hrt_finite(lr.o.y) && hrt_finite(lr.o.z))) { b.bad = 1; return; }
-        }
-        if (m.fast_root >= 0) {          // whole-mesh rejection before any per-ray triangle set-up: most camera rays miss the mesh
-            const float4* N = m.fast_nodes + 4 * (size_t)m.fast_root;
-            float tn0, tf0, tn1, tf1;
-            slab2(HRT_LD4(N), HRT_LD4(N + 1), HRT_LD4(N + 2), lr.o, id, tn0, tf0, tn1, tf1);
-            const float t_lo = fminf(t_min, 0.0f);
-            if (!(tn0 <= tf0 && tf0 >= t_lo) && !(tn1 <= tf1 && tf1 >= t_lo)) return;
-        }
-        const int kZ = tri_kz(lr.o);
-        if (!COLLECT && !shear_ok(lr, kZ)) { b.shear = 1; return; }             // pass 2 will collect every hit along this ray
-#if HRT_KZ_MODE == 1
-        mesh_walk<3, COLLECT, COUNT>(m, lr, id, kZ, t_min, b, k, i, cnt);
-#else
-#if HRT_KZ_MODE == 2 && defined(__CUDA_ARCH__)
-        if (!__all_sync(__activemask(), kZ == __shfl_sync(__activemask(), kZ, __ffs(__activemask()) - 1))) {
-            mesh_walk<3, COLLECT, COUNT>(m, lr, id, kZ, t_min, b, k, i, cnt);
-            return;
-        }
-#endif
-        switch (kZ) {
-        case 0: mesh_walk<0, COLLECT, COUNT>(m, lr, id, 0, t_min, b, k, i, cnt); break;
-        case 1: mesh_walk<1, COLLECT, COUNT>(m, lr, id, 1, t_min, b, k, i, cnt); break;
-        default: mesh_walk<2, COLLECT, COUNT>(m, lr, id, 2, t_min, b, k, i, cnt); break;
-        }
-#endif
-        return;
-    }
-    float t; uint32_t prim;
-    if (COUNT) cnt->prims += 1;
-    if (hit_object_ref(s, i, r, t_min, COLLECT ? k.beta : cull_bound(b), t, prim, key, bounce)) {
-        if (COLLECT) collect(k, t, i, prim, 0u); else consider(b, t, t, prim, i);
-    }
-}
+// ---- one loop over both levels ---------------------------------------------------------------------------------------------
+// Top level: SAH tree over world-list entries.  Bottom level: per-mesh SAH tree over the reference's bottom nodes (a leaf
+// is one bottom node of bvh.cpp's topology: its 1-2 triangles are tested with exact ITriangle arithmetic, and the
+// reference's own slab test of the node box — six IEEE divisions — is only evaluated for a triangle that was accepted:
+// it decides whether the reference could have reached the triangle at this bound and yields entry_i).
+// Both levels share one stack and ONE node loop: entering a mesh pushes a marker, swaps in the local ray and carries on
+// with the mesh's nodes; popping the marker swaps the world ray back.  With a walk function per level (r1c) the lanes of
+// a warp reached a mesh in different iterations of the top-level loop and in three kZ instantiations, and the mesh walk
+// ran with 1.5-2.3 active lanes of 32 on scenes where most rays reach a mesh (profiles/ r1d, teapot_scene).
+// COLLECT = false: pass 1 (track the best candidate, cull by it).  COLLECT = true: pass 2 (fixed bound k.beta, every
+// candidate goes to the collector).
+constexpr int WALK_MARK = (int)0x80000000;     // stack marker: "leave the mesh"; never a node (>= 0) nor ~index of anything
+constexpr int WALK_STACK = 48 + FAST_MAX_DEPTH + 8;
 
-// ---- top level: SAH tree over world-list entries ----------------------------------------------------------------------------
 template <bool COLLECT, bool COUNT>
-HRT_HDN inline void world_walk(const DScene& s, const Ray& r, const V3 id, float t_min, Best& b, Collector& k, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
+HRT_HDN inline void world_walk(const DScene& s, const Ray& r, const V3 rid, float t_min, Best& b, Collector& k, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
 {
     // RotateQuat objects report t in units of their normalised direction (rotateQuat.cpp:51):
     // reported t >= world t * |d| * tlas_cull_scale, so entry distances are scaled down before they cull.
-    const float cull = s.tlas_cull_scale > 0.0f ? fminf(1.0f, length(r.d) * s.tlas_cull_scale) * 0.9999f : 1.0f;
-    const float t_lo = fminf(t_min, 0.0f);
-    int stack[48]; int sp = 0;
+    const float cull_top = s.tlas_cull_scale > 0.0f ? fminf(1.0f, length(r.d) * s.tlas_cull_scale) * 0.9999f : 1.0f;
+    const float t_lo = fminf(t_min, 0.0f);            // ITriangle::hit ignores t_min but only reports t > 0
+    int stack[WALK_STACK]; int sp = 0;
+    // current level: ray the nodes are tested against, node array, cull scale
+    V3 co = r.o, cid = rid; float cull = cull_top;
+    const float4* nodes = s.tlas_nodes;
+    // mesh level state
+    int obj = -1; Ray lr = r; TriRay q; q.o = r.o; q.sX = q.sY = q.sZ = 0.0f; q.kz = 2; bool q_ready = false;
+    const float4* leaves = nullptr; uint32_t prim_base = 0;
     int node = s.tlas_root;
     for (;;) {
-        if (node >= 0) {
-            const float4* N = s.tlas_nodes + 4 * (size_t)node;
+        while (node >= 0) {                                                    // inner nodes of either level
+            const float4* N = nodes + 4 * (size_t)node;
             float4 n0 = HRT_LD4(N), n1 = HRT_LD4(N + 1), n2 = HRT_LD4(N + 2), n3 = HRT_LD4(N + 3);
             float tn0, tf0, tn1, tf1;
-            slab2(n0, n1, n2, r.o, id, tn0, tf0, tn1, tf1);
+            slab2(n0, n1, n2, co, cid, tn0, tf0, tn1, tf1);
             if (COUNT) cnt->nodes += 2;
             const float bound = COLLECT ? k.beta : cull_bound(b);
             bool h0 = tn0 <= tf0 && tf0 >= t_lo && (tn0 <= 0.0f || tn0 * cull <= bound);
@@ -268,15 +176,70 @@ HRT_HDN inline void world_walk(const DScene& s, const Ray& r, const V3 id, float
             int c0 = float_as_int(n3.x), c1 = float_as_int(n3.y);
             if (h0 && h1) {
                 if (tn1 < tn0) { int tmp = c0; c0 = c1; c1 = tmp; }
-                if (sp < 47) stack[sp++] = c1; else b.bad = 1;
-                node = c0; continue;
-            }
-            if (h0) { node = c0; continue; }
-            if (h1) { node = c1; continue; }
-        } else {
-            object_walk<COLLECT, COUNT>(s, ~node, r, id, t_min, b, k, key, bounce, cnt);
+                if (sp < WALK_STACK - 2) stack[sp++] = c1; else b.bad = 1;
+                node = c0;
+            } else if (h0) node = c0;
+            else if (h1) node = c1;
+            else { if (sp == 0) return; node = stack[--sp]; }
         }
-        if (sp == 0 || b.bad) break;
+        if (node == WALK_MARK) {                                               // the mesh is done: back to the world ray
+            co = r.o; cid = rid; cull = cull_top; nodes = s.tlas_nodes; obj = -1;
+        } else if (obj >= 0) {                                                 // a leaf of the mesh tree
+            const uint32_t leaf = (uint32_t)(~node);
+            const float4* L = leaves + 8 * (size_t)leaf;
+            const float4 a = HRT_LD4(L), c = HRT_LD4(L + 1);
+            const int triL = float_as_int(a.w), triR = float_as_int(c.w);
+            if (!q_ready) { q = tri_ray<3>(lr, tri_kz(lr.o)); q_ready = true; }
+            const float bound = COLLECT ? k.beta : cull_bound(b);
+            float tL = 0, tR = 0;
+            if (COUNT) cnt->prims += (triR != triL) ? 2 : 1;
+            bool hL = itriangle_t<3>(HRT_LD4(L + 2), HRT_LD4(L + 3), HRT_LD4(L + 4), q, bound, tL);
+            bool hR = triR != triL && itriangle_t<3>(HRT_LD4(L + 5), HRT_LD4(L + 6), HRT_LD4(L + 7), q, bound, tR);
+            if (hL || hR) {
+                float entry;
+                if (COUNT) cnt->nodes += 1;
+                if (hit_aabb_entry(xyz(a), xyz(c), lr, t_min, bound, entry)) {       // the reference's bottom node box, its arithmetic
+                    if (COLLECT) {
+                        if (hL) collect(k, tL, obj, prim_base + (uint32_t)triL, leaf * 2u);
+                        if (hR) collect(k, tR, obj, prim_base + (uint32_t)triR, leaf * 2u + 1u);
+                    } else {
+                        if (hL) consider(b, tL, fmaxf(entry, tL), prim_base + (uint32_t)triL, obj);
+                        if (hR) consider(b, tR, fmaxf(entry, tR), prim_base + (uint32_t)triR, obj);   // beyond the new bound: no effect
+                    }
+                }
+            }
+        } else {                                                               // a world-list entry
+            const int i = ~node;
+            const DObject& ob = s.objects[i];
+            if (ob.kind == SHAPE_MESH && !ob.medium) {
+                const DMesh& m = s.meshes[ob.mesh];
+                if (m.ref_root >= 0) {
+                    // the three IEEE reciprocals of a ray are computed once per coordinate frame: an unwrapped mesh shares the world ray's
+                    lr = r; V3 id = rid; bool ok = true;
+                    if (ob.xf_count > 0) {
+                        lr = to_local(s, ob, r);
+                        id = v3(1.0f / lr.d.x, 1.0f / lr.d.y, 1.0f / lr.d.z);
+                        ok = recip_ok(id) && hrt_finite(lr.o.x) && hrt_finite(lr.o.y) && hrt_finite(lr.o.z);
+                    }
+                    if (!ok) b.bad = 1;
+                    else if (!COLLECT && !shear_ok(lr, tri_kz(lr.o))) b.shear = 1;      // pass 2 will collect every hit along this ray
+                    else {
+                        if (sp < WALK_STACK - 2) stack[sp++] = WALK_MARK; else b.bad = 1;
+                        co = lr.o; cid = id; cull = 1.0f; nodes = m.fast_nodes; leaves = m.fast_leaves; prim_base = m.prim_base;
+                        obj = i; q_ready = false;
+                        node = m.fast_root;                                     // >= 0 node, < 0 leaf: handled by the next turn of the loop
+                        if (!b.bad) continue;
+                    }
+                }
+            } else {
+                float t; uint32_t prim;
+                if (COUNT) cnt->prims += 1;
+                if (hit_object_ref(s, i, r, t_min, COLLECT ? k.beta : cull_bound(b), t, prim, key, bounce)) {
+                    if (COLLECT) collect(k, t, i, prim, 0u); else consider(b, t, t, prim, i);
+                }
+            }
+        }
+        if (sp == 0 || b.bad) return;
         node = stack[--sp];
     }
 }

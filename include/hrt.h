@@ -111,6 +111,7 @@ typedef struct hrt_render_params {
 } hrt_render_params;
 
 #define HRT_RENDER_MEGAKERNEL 1   /* one thread per path instead of the persistent wavefront (debug/validation) */
+#define HRT_RENDER_WAVEFRONT_V1 2  /* every camera ray goes through the queues (the r1b/r1c pipeline, kept for A/B runs) */
 
 typedef struct hrt_stats {
     uint64_t rays;            /* closest-hit queries issued (= world->hit calls of main.cpp:45)      */

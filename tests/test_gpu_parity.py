@@ -195,6 +195,9 @@ def test_wavefront_equals_megakernel_and_sample_split(hrt, cache_dir):
         wf, _ = g.render(c, w, h, spp, seed=9)
         mk, _ = g.render(c, w, h, spp, seed=9, flags=abi.RENDER_MEGAKERNEL)
         assert np.array_equal(bits(wf), bits(mk)), "wavefront pipeline differs from the one-thread-per-path loop"
+        v1, _ = g.render(c, w, h, spp, seed=9, flags=abi.RENDER_WAVEFRONT_V1)
+        assert np.array_equal(bits(wf), bits(v1)), "fused-primary pipeline differs from the every-ray-queued pipeline"
+        assert g.stats().rays % 3 == 0              # three renders of the same paths counted the same rays
         # samples are keyed by (pixel, global sample index) and the film adds integers: the wavefront capacity (hence the
         # order in which paths start and finish) does not change a single bit
         for cap in (1024, 5000):

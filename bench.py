@@ -51,8 +51,9 @@ def make_workload(name, args):
 
 
 def alg_bytes_per_ray(sd):
-    """Algorithmic bytes of one closest-hit query in the traversal kernel: 32 B ray read + 16 B hit
-    written + one root-to-leaf path of 32 B nodes + one primitive (48 B triangle / 16 B sphere / 32 B rect)."""
+    """B_alg = B_state (176 B of ray / hit / path-state streams) + one root-to-leaf path of 32 B nodes
+    + one primitive (48 B triangle / 16 B sphere / 32 B rect).  Input-determined: it does not shrink when the kernel
+    keeps a camera path in registers instead of streaming it."""
     n_prims = 0; prim_bytes = 16
     for s in sd.shapes:
         if s[0] == "mesh":
@@ -64,7 +65,7 @@ def alg_bytes_per_ray(sd):
             if s[0] == "rect":
                 prim_bytes = max(prim_bytes, 32)
     depth = int(np.ceil(np.log2(max(n_prims, 2))))
-    return 32 + 16 + 32 * depth + prim_bytes, n_prims
+    return 176 + 32 * depth + prim_bytes, n_prims
 
 
 class ClockSampler:
@@ -260,14 +261,14 @@ def run_own(args):
                 "samples_per_s": paths / (ms * 1e-3), "samples_per_s_per_gpu": paths / (ms * 1e-3) / world, "rays_per_sample": rays / max(paths, 1),
                 "config": {"workload": f"{info['name']} {w}x{h}, {spp} spp split over {world} GPU(s)", "width": w, "height": h, "spp": spp, "max_depth": 50,
                            "bvh": args.bvh, "n_prims": n_prims, "pipeline": "megakernel" if args.megakernel else ("persistent wavefront, every ray queued" if args.pipeline == "v1" else "wavefront, camera paths fused into the trace pass"),
-                           "cache": "the wavefront queues (4 Mi entries: rays + hits + path state = 600 MB) exceed the 126 MB L2 and are rewritten every pass; no flush needed"},
+                           "cache": "camera paths are generated on the device every step (nothing to reuse); between steps the 66 MB film is re-zeroed and the 600 MB of queues rewritten, both larger than L2 with the 33 MB scene; no flush needed"},
                 "e2e": {"value": float(e2e_r.item()) / float(e2e_s.item()) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": scene_bytes,
                         "d2h_bytes_per_step": npix * 15, "steps": e2e_steps, "includes": "scene build + BVH build + upload, render, float film + 8-bit image read-back"},
                 "gpu_launches": int(launches), "commit_s": t_commit, "replayed_fraction": float(st.retraced) / max(float(st.rays), 1.0), "ref_walk_rays": int(st.prim_tests),
                 "kernel_ms": {"trace": st.ms_trace, "shade": st.ms_shade, "other": st.ms_other, "total": st.ms_total, "note": "rank 0, CUDA events inside the timed region"},
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": (ach / peak) if ach else None, "traffic": traffic,
-                             "kernel": "k_wave_trace", "alg_bytes_per_ray": b_alg, "peak_source": peak_src,
-                             "note": "latency/divergence-bound pointer chasing; scene fits L2, see DESIGN.md"},
+                             "kernel": "k_wave_trace" if args.pipeline == "v1" else "k_wave2_trace", "alg_bytes_per_ray": b_alg, "trace_launches": int(st.launches) // 2, "peak_source": peak_src,
+                             "note": "achieved = rays x B_alg / device time of the traversal kernel (CUDA events); the scene is L1/L2 resident and camera paths live in registers, so DRAM traffic is far below the algorithmic bytes: the kernel is issue/latency bound, see DESIGN.md"},
                 "clocks": clk}
         if world == 1 and not args.no_cpu:
             try:

@@ -63,6 +63,7 @@ struct hrt_scene {
     // ray-batch working set
     float4* tb_rays = nullptr; Hit* tb_hits = nullptr;
     uint32_t* tb_prim = nullptr; float* tb_t = nullptr; long long tb_capacity = 0;
+    unsigned long long* d_counter = nullptr;                    // ray hand-out counter of k_trace_batch
     hrt_stats stats{};
     bool last_secondary_heavy = false;
 };
@@ -105,6 +106,7 @@ int ensure_job(hrt_scene* s, unsigned int capacity)
 }
 int ensure_tb(hrt_scene* s, long long n, bool own_rays)
 {
+    if (!s->d_counter) CK(cudaMalloc(&s->d_counter, sizeof(unsigned long long)));
     if (n > s->tb_capacity) {
         free_tb(s);
         CK(cudaMalloc(&s->tb_rays, sizeof(float4) * 2 * (size_t)n));
@@ -261,7 +263,7 @@ void hrt_scene_destroy(hrt_scene* s)
     if (s->host.committed || s->stream) {
         cudaSetDevice(s->device);
         free_job(s); free_tb(s); free_scene_device(s);
-        cudaFree(s->d_film); cudaFree(s->d_out);
+        cudaFree(s->d_film); cudaFree(s->d_out); cudaFree(s->d_counter);
         if (s->h_ctl) cudaFreeHost(s->h_ctl);
         for (cudaEvent_t e : s->events) cudaEventDestroy(e);
         if (s->stream) cudaStreamDestroy(s->stream);
@@ -302,6 +304,7 @@ int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed)
     CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
     DevUp up(s->scene_allocs);
     s->d = make_dscene(s->host, up);
+    if (const char* e = getenv("HRT_REFILL_SECONDARY")) s->d.refill_secondary = (atoi(e) != 0 && s->d.fast) ? 1 : 0;   // A/B override
     if (up.failed) { g_err = "scene upload failed: " + up.msg; free_scene_device(s); return HRT_ERR_CUDA; }
     s->scene_bytes = up.bytes;
     CK(cudaDeviceSynchronize());
@@ -320,7 +323,7 @@ int hrt_trace_batch_device(hrt_scene* s, const void* d_rays, int64_t n, void* d_
     if (n > s->tb_capacity) {                      // only hits / retrace list are needed for a device call; allocate the full set for simplicity
         int rc = ensure_tb(s, n, false); if (rc < 0) return rc;
     }
-    launch_trace_batch(s->d, (const float4*)d_rays, n, s->tb_hits, rng_seed, s->sm_count, st, &s->stats.launches);
+    launch_trace_batch(s->d, (const float4*)d_rays, n, s->tb_hits, rng_seed, s->d_counter, s->sm_count, st, &s->stats.launches);
     launch_split_hits(s->tb_hits, n, (uint32_t*)d_prim_id, (float*)d_t, s->sm_count, st, &s->stats.launches);
     CK(cudaGetLastError());
     s->stats.rays += (uint64_t)n;

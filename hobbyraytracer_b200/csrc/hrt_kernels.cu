@@ -34,14 +34,49 @@ __device__ __forceinline__ RngKey make_key(uint64_t seed, uint32_t index, uint32
 #ifndef HRT_BATCH_MIN_BLOCKS
 #define HRT_BATCH_MIN_BLOCKS 8      // 16 M incoherent rays vs 10.5 M triangles on B200: 523 (4 blocks) / 591 (6) / 709 (8) Mrays/s
 #endif
-__global__ void __launch_bounds__(BLOCK, HRT_BATCH_MIN_BLOCKS) k_trace_batch(DScene s, const float4* __restrict__ rays, long long n, Hit* __restrict__ hits, uint64_t seed)
+#ifndef HRT_REFILL_THRESH
+#define HRT_REFILL_THRESH 24        // a warp goes back for new rays as soon as fewer than this many lanes are still walking
+#endif
+// Persistent warps with per-lane refill: a lane whose walk is over takes the next ray from a global counter while the
+// other lanes keep the state of theirs (Walk), so the warp's node loop stays full whatever the spread of walk lengths.
+__global__ void __launch_bounds__(BLOCK, HRT_BATCH_MIN_BLOCKS) k_trace_batch(DScene s, const float4* __restrict__ rays, long long n, Hit* __restrict__ hits, uint64_t seed,
+                                                                            unsigned long long* __restrict__ counter)
 {
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        float4 a = __ldg(rays + 2 * i), b = __ldg(rays + 2 * i + 1);
-        Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
-        RngKey key = make_key(seed, (uint32_t)i, (uint32_t)(i >> 32), 0);
-        hits[i] = s.fast ? trace_fast<false>(s, r, a.w, b.w, key, 0, nullptr) : trace_ref(s, r, a.w, b.w, key, 0);
+    if (!s.fast) {                                                                // reference visiting order: one ray per thread
+        const long long stride = (long long)gridDim.x * blockDim.x;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+            float4 a = __ldg(rays + 2 * i), b = __ldg(rays + 2 * i + 1);
+            Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
+            hits[i] = trace_ref(s, r, a.w, b.w, make_key(seed, (uint32_t)i, (uint32_t)(i >> 32), 0), 0);
+        }
+        return;
+    }
+    const unsigned int lane = threadIdx.x & 31u;
+    Walk w; w.live = false; w.pre = 1;
+    long long idx = -1; bool exhausted = false;
+    Collector* none = nullptr;
+    for (;;) {
+        const bool need = idx < 0;
+        const unsigned int m = __ballot_sync(0xffffffffu, need);
+        if (m && !exhausted) {
+            unsigned long long base = 0;
+            if (lane == (unsigned int)(__ffs(m) - 1)) base = atomicAdd(counter, (unsigned long long)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+            if (need) {
+                const long long my = (long long)base + __popc(m & ((1u << lane) - 1u));
+                if (my < n) {
+                    idx = my;
+                    float4 a = __ldg(rays + 2 * my), b = __ldg(rays + 2 * my + 1);
+                    Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
+                    trace_begin(w, s, r, a.w, b.w);
+                }
+            }
+            if ((long long)base + __popc(m) >= n) exhausted = true;
+        }
+        if (!__any_sync(0xffffffffu, idx >= 0)) break;
+        const RngKey key = make_key(seed, (uint32_t)idx, (uint32_t)((unsigned long long)idx >> 32), 0);
+        walk_run<false, false, true>(w, s, *none, key, 0, nullptr, exhausted ? 1 : HRT_REFILL_THRESH);
+        if (idx >= 0 && !w.live) { hits[idx] = trace_finish<false>(w, s, key, 0, nullptr); idx = -1; }
     }
 }
 __global__ void __launch_bounds__(BLOCK) k_split_hits(const Hit* __restrict__ hits, long long n, uint32_t* __restrict__ prim, float* __restrict__ t)
@@ -302,8 +337,52 @@ __device__ __forceinline__ void acc_flush(FilmAcc& a, long long* film, int pix)
 // Two builds of the same kernel: 128 registers / 4 blocks per SM when camera paths dominate (shiny_teapot: +8 %), 64 registers /
 // 8 blocks per SM when incoherent secondary rays dominate (cornell, scattered balls, teapot_scene: +7-11 %; latency hiding
 // beats spilling there).  The host picks per chunk from the secondary-rays-per-camera-path ratio it reads in the control block.
+// Secondary rays of queue q with per-lane refill (scenes with meshes: the walks are long and their lengths spread widely).
+// Runs before k_wave2_trace, which is then told to skip its own lock-step pass over these entries.
+#ifndef HRT_DYN_MIN_BLOCKS
+#define HRT_DYN_MIN_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(BLOCK, HRT_DYN_MIN_BLOCKS) k_wave2_secondary(DScene s, WaveJob j, int q)
+{
+    WaveCtl* c = j.ctl;
+    const unsigned int n_sec = c->n_front[q];
+    if (n_sec == 0) return;
+    const unsigned int lane = threadIdx.x & 31u;
+    const float4* __restrict__ rays = j.rays[q];
+    Walk w; w.live = false; w.pre = 1;
+    bool have = false, exhausted = false;
+    unsigned int e_idx = 0, st = 0; int pix = 0;
+    Collector* none = nullptr;
+    for (;;) {
+        const bool need = !have;
+        const unsigned int m = __ballot_sync(0xffffffffu, need);
+        if (m && !exhausted) {
+            unsigned int base = 0;
+            if (lane == (unsigned int)(__ffs(m) - 1)) base = atomicAdd(&c->sec_next[q], (unsigned int)__popc(m));
+            base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+            const unsigned int my = base + (unsigned int)__popc(m & ((1u << lane) - 1u));
+            if (need && my < n_sec) {
+                float4 a = rays[2 * (size_t)my], b = rays[2 * (size_t)my + 1];
+                Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
+                pix = __float_as_int(a.w); st = __float_as_uint(b.w);
+                e_idx = my; have = true;
+                trace_begin(w, s, r, j.t_min, hrt_inf());
+            }
+            if (base + (unsigned int)__popc(m) >= n_sec) exhausted = true;
+        }
+        if (!__any_sync(0xffffffffu, have)) break;
+        const RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + (int)((st >> 8) & 0x7fffffu)), j.rng_mode);
+        walk_run<false, false, true>(w, s, *none, key, st & 0xffu, nullptr, exhausted ? 1 : HRT_REFILL_THRESH);
+        if (have && !w.live) {
+            const Hit h = trace_finish<false>(w, s, key, st & 0xffu, nullptr);
+            if (h.flags & (HIT_RESOLVED | HIT_FALLBACK)) atomicAdd((h.flags & HIT_FALLBACK) ? &c->fallbacks : &c->resolved, 1ull);
+            j.hits[e_idx] = h; have = false;
+        }
+    }
+}
+
 template <int MINB>
-__global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j, DCamera cam, int q)
+__global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j, DCamera cam, int q, int skip_secondary)
 {
     WaveCtl* c = j.ctl;
     const unsigned int n_sec = c->n_front[q];
@@ -316,7 +395,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j
     const unsigned int margin = warps_total * (unsigned int)CLAIM;                // what the other warps may still append after a check
     const unsigned int n_units = wave2_units(j);
     float4* __restrict__ rays = j.rays[q];
-    unsigned int sec_i = (blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5)) * 32u + lane;
+    unsigned int sec_i = skip_secondary ? n_sec + lane : (blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5)) * 32u + lane;   // skip: k_wave2_secondary did them
     int c_left = 0, c_sl = 0, c_pix = -1, c_x = 0, c_y = 0;                         // the warp's claim: pixel of this lane, next sample, samples left
     FilmAcc acc; acc.q[0] = acc.q[1] = acc.q[2] = 0; acc.flags = 0;
     for (;;) {
@@ -396,7 +475,7 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave2_shade(DScene s, WaveJob j
     WaveCtl* c = j.ctl;
     const int o = q ^ 1;
     const unsigned int n = c->n_front[q] + c->n_prim[q];
-    if (blockIdx.x == 0 && threadIdx.x == 0) c->n_prim[o] = 0;                    // the next trace pass appends to queue o; nobody reads this here
+    if (blockIdx.x == 0 && threadIdx.x == 0) { c->n_prim[o] = 0; c->sec_next[o] = 0; }   // the next trace pass works on queue o; nobody reads these here
     const float4* __restrict__ rays = j.rays[q];
     const unsigned int lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const unsigned int stride = gridDim.x * SHADE_BLOCK;
@@ -476,9 +555,10 @@ int grid_for(long long n, int sm_count, int per_sm)
 } // namespace
 
 // ---- launchers -------------------------------------------------------------------------------------------------------------
-void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed, int sm_count, cudaStream_t st, uint64_t* launches)
+void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed, unsigned long long* d_counter, int sm_count, cudaStream_t st, uint64_t* launches)
 {
-    k_trace_batch<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed); *launches += 1;
+    cudaMemsetAsync(d_counter, 0, sizeof(unsigned long long), st);
+    k_trace_batch<<<grid_for(n, sm_count, s.fast ? HRT_BATCH_MIN_BLOCKS : 16), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed, d_counter); *launches += 1;
 }
 void launch_split_hits(const Hit* d_hits, long long n, uint32_t* d_prim, float* d_t, int sm_count, cudaStream_t st, uint64_t* launches)
 {
@@ -517,8 +597,12 @@ int wave2_trace_blocks(unsigned int capacity, int sm_count, int minb)
 unsigned long long wave2_total_claims(const WaveJob& j) { return (unsigned long long)wave2_units(j) * (unsigned long long)wave2_sblocks(j); }
 void launch_wave2_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, bool secondary_heavy, int sm_count, cudaStream_t st, uint64_t* launches)
 {
-    if (secondary_heavy) k_wave2_trace<8><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1);
-    else k_wave2_trace<4><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1);
+    // per-lane refill pass first when the scene has meshes AND secondary rays dominate (A/B on B200, Mrays/s with / without:
+    // teapot_scene 1199 / 997, but shiny_teapot 7194 / 7715 and the 2.9 M-triangle big mesh 2000 / 2144, whose secondary rays mostly leave at once)
+    const int refill = s.refill_secondary && secondary_heavy;
+    if (refill) { k_wave2_secondary<<<sm_count * HRT_DYN_MIN_BLOCKS, BLOCK, 0, st>>>(s, j, it & 1); *launches += 1; }
+    if (secondary_heavy) k_wave2_trace<8><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
+    else k_wave2_trace<4><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
     *launches += 1;
 }
 void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches)

@@ -20,6 +20,7 @@ struct WaveCtl {
     unsigned long long rays;            // closest-hit queries issued
     unsigned long long resolved;        // rays answered by pass 2 + replay (hrt_trace.cuh)
     unsigned long long fallbacks;       // rays answered by trace_ref
+    unsigned int sec_next[2];           // fused-primary pipeline: hand-out counter of the secondary entries of queue q (per-lane refill)
     unsigned int n_prim[2];             // fused-primary pipeline: camera-path hits appended behind the n_front[q] secondary entries of queue q
     float dbg[16][8];                   // first rays that took the trace_ref fallback (o, pixel, d, state), for diagnosis
 };
@@ -47,7 +48,7 @@ struct WaveJob {
     long long* film;                    // npix * FILM_LANES
 };
 
-void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed, int sm_count, cudaStream_t st, uint64_t* launches);
+void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed, unsigned long long* d_counter, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_split_hits(const Hit* d_hits, long long n, uint32_t* d_prim, float* d_t, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_eval_batch(const DScene& s, const float4* d_rays, const Hit* d_hits, long long n, float* d_normal, float* d_uv, uint8_t* d_front,
                        int sm_count, cudaStream_t st, uint64_t* launches);

@@ -52,6 +52,7 @@ DScene make_dscene(HostScene& s, Up& up)
     d.n_textures = (int)s.textures.size();
     d.background = s.background;
     d.fast = fast ? 1 : 0;
+    d.refill_secondary = (fast && !meshes.empty()) ? 1 : 0;
     d.tlas_cull_scale = s.tlas_cull_scale;
     d.nan_obj = -1; d.nan_prim = HRT_MISS;
     for (int i = (int)s.d_objects.size() - 1; i >= 0 && d.nan_obj < 0; --i) {

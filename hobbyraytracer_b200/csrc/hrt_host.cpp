@@ -15,6 +15,7 @@
 #include <cstring>
 #include <limits>
 #include <map>
+#include <mutex>
 #include <thread>
 
 namespace hrt {
@@ -338,11 +339,29 @@ void build_fast_bvh(const std::vector<float>& bmin, const std::vector<float>& bm
 // Exact repack of a decoded Radiance image (texture.cpp:99-115 -> stb_image stbi__hdr_convert: byte * 2^(e-136))
 // into one 32-bit word per texel; refuses (returns false) unless every texel round-trips bit for bit.
 // ------------------------------------------------------------------------------------------------------------
+namespace {
+std::mutex g_pool_mutex;
+std::vector<uint32_t> g_pool;                      // one spare buffer (the most recently returned one)
+}
+std::vector<uint32_t> take_words(size_t n)
+{
+    std::vector<uint32_t> v;
+    { std::lock_guard<std::mutex> lock(g_pool_mutex); v.swap(g_pool); }
+    v.resize(n);                                   // same size as last time: nothing is filled, the pages are already mapped
+    return v;
+}
+void give_words(std::vector<uint32_t>&& v)
+{
+    if (v.capacity() > (size_t(1) << 28)) return;   // keep at most 1 GiB around
+    std::lock_guard<std::mutex> lock(g_pool_mutex);
+    if (v.capacity() >= g_pool.capacity()) g_pool.swap(v);
+}
+
 bool try_pack_rgbe(const float* f32, int w, int h, int ch, std::vector<uint32_t>& rgbe)
 {
     if (!f32 || ch < 3 || w <= 0 || h <= 0) return false;
     const size_t n = (size_t)w * h;
-    rgbe.resize(n);
+    rgbe = take_words(n);
     std::atomic<bool> ok{true};
     // Integer form of "p == q * 2^(e-136) with q an integer in [0,255]": with mexp the biased exponent of the largest
     // channel, e = mexp + 2 (= frexp exponent + 128) and a channel 1.mant * 2^(cexp-127) is q = 1.mant * 2^(cexp-mexp+7).
@@ -373,7 +392,7 @@ bool try_pack_rgbe(const float* f32, int w, int h, int ch, std::vector<uint32_t>
     for (int t = 1; t < nt; ++t) th.emplace_back(work, n * (size_t)t / (size_t)nt, n * (size_t)(t + 1) / (size_t)nt);
     work(0, n / (size_t)nt);
     for (auto& t : th) t.join();
-    if (!ok) { rgbe.clear(); rgbe.shrink_to_fit(); return false; }
+    if (!ok) { give_words(std::move(rgbe)); rgbe = std::vector<uint32_t>(); return false; }
     return true;
 }
 

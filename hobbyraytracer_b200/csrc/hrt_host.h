@@ -9,6 +9,11 @@
 
 namespace hrt {
 
+// Recycled word buffers for packed environment maps: a fresh 32 MiB allocation costs more in page faults (zero fill + first
+// touch, ~20 ms on the GPU box) than packing into it; scenes are typically rebuilt with an environment of the same size.
+std::vector<uint32_t> take_words(size_t n);
+void give_words(std::vector<uint32_t>&& v);
+
 struct HostTexture {
     int kind = TEX_SOLID;
     float rgb[3] = {0, 0, 0};
@@ -17,6 +22,12 @@ struct HostTexture {
     std::vector<uint8_t> u8;
     std::vector<float> f32;
     std::vector<uint32_t> rgbe;     // env maps whose every texel is exactly RGBE-representable are kept ONLY in this form (f32 stays empty)
+    HostTexture() = default;
+    HostTexture(HostTexture&&) = default;
+    HostTexture& operator=(HostTexture&&) = default;
+    HostTexture(const HostTexture&) = default;
+    HostTexture& operator=(const HostTexture&) = default;
+    ~HostTexture() { if (!rgbe.empty()) give_words(std::move(rgbe)); }
 };
 
 struct RefBvh {                      // bvh.cpp:6-61 in index form

@@ -32,6 +32,23 @@ ORACLE_SO = os.path.join(ROOT, "oracle", "_build", "liboracle.so")
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "libhrt_ref.so")
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """The contract is ONE JSON line on stdout; libraries (NCCL prints its version there) get stderr instead."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n"); out.flush()
+
+
 def make_workload(name, args):
     """-> (SceneDesc, camera dict, width, height, spp, n_prims-for-B_alg, prim bytes)"""
     if name == "shiny_teapot":
@@ -152,7 +169,7 @@ def run_reference(args):
             "config": {"workload": f"{info['name']} {w}x{h}, {info['spp']} spp (CPU arm: bounded sample per step)", "width": w, "height": h, "spp": info["spp"]},
             "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -184,7 +201,17 @@ def run_own(args):
     stream = torch.cuda.current_stream().cuda_stream
     flags = abi.RENDER_MEGAKERNEL if args.megakernel else (abi.RENDER_WAVEFRONT_V1 if args.pipeline == "v1" else 0)
 
+    pf = None
+    if world > 1 and args.reduce == "peer":
+        pf = multigpu.PeerFilm(sc, w, h, rank, world, dist)
+        if not pf.ok:                                   # no CUDA IPC / peer access on this box: NCCL reduce (still a GPU path)
+            pf.close(); pf = None
+    reduce_kind = "none (1 GPU)" if world == 1 else ("in-kernel sum over NVLink peer memory (CUDA IPC), fused with the resolve" if pf else "NCCL reduce(SUM, int64) + resolve")
+
     def step():
+        if pf is not None:
+            multigpu.render_split_peer(pf, c, spp, seed=args.seed, stream_ptr=stream, rgb8=rgb8, total=fsum, flags=flags)
+            return
         film.zero_()
         multigpu.render_split(sc, c, w, h, spp, film, rank, world, dist, seed=args.seed, stream_ptr=stream, rgb8=rgb8, flags=flags)
 
@@ -260,7 +287,7 @@ def run_own(args):
                 "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "samples_per_s": paths / (ms * 1e-3), "samples_per_s_per_gpu": paths / (ms * 1e-3) / world, "rays_per_sample": rays / max(paths, 1),
                 "config": {"workload": f"{info['name']} {w}x{h}, {spp} spp split over {world} GPU(s)", "width": w, "height": h, "spp": spp, "max_depth": 50,
-                           "bvh": args.bvh, "n_prims": n_prims, "pipeline": "megakernel" if args.megakernel else ("persistent wavefront, every ray queued" if args.pipeline == "v1" else "wavefront, camera paths fused into the trace pass"),
+                           "bvh": args.bvh, "n_prims": n_prims, "film_reduce": reduce_kind, "pipeline": "megakernel" if args.megakernel else ("persistent wavefront, every ray queued" if args.pipeline == "v1" else "wavefront, camera paths fused into the trace pass"),
                            "cache": "camera paths are generated on the device every step (nothing to reuse); between steps the 66 MB film is re-zeroed and the 600 MB of queues rewritten, both larger than L2 with the 33 MB scene; no flush needed"},
                 "e2e": {"value": float(e2e_r.item()) / float(e2e_s.item()) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": scene_bytes,
                         "d2h_bytes_per_step": npix * 15, "steps": e2e_steps, "includes": "scene build + BVH build + upload, render, float film + 8-bit image read-back"},
@@ -277,7 +304,7 @@ def run_own(args):
                                         "samples_per_s": r["samples"] / r["seconds"]}
             except Exception as e:  # the checker is missing: say so, never substitute
                 line["cpu_baseline"] = {"value": None, "unit": "Mrays/s", "cores": 0, "kind": "unavailable", "sample": str(e)}
-        print(json.dumps(line))
+        emit(line)
     if dist is not None:
         dist.barrier(); dist.destroy_process_group()
 
@@ -342,7 +369,7 @@ def run_raybatch(args):
         b_alg, n_prims = alg_bytes_per_ray(sd)
         rate = n * world * args.steps / (ms * 1e-3)
         st = sc.stats()
-        print(json.dumps({"metric": "Mrays/s", "value": rate / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        emit({"metric": "Mrays/s", "value": rate / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                           "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                           "config": {"workload": f"ray batch: {n_total} incoherent rays vs {n_prims}-triangle mesh, split over {world} GPU(s)", "n_prims": n_prims,
                                      "rays": n_total, "cache": "16 M rays x 32 B = 512 MB per step, larger than L2"},
@@ -350,7 +377,7 @@ def run_raybatch(args):
                           "gpu_launches": int(st.launches), "commit_s": t_commit, "build_ms": st.ms_build, "scene_bytes": int(st.scene_bytes),
                           "parity": {"sah_equals_reference_order": same, "rays_checked": k, "hit_rate": hit_rate},
                           "roofline": {"bound": "hbm", "achieved": rate / world * b_alg / 1e9, "peak": peak, "unit": "GB/s", "frac": rate / world * b_alg / 1e9 / peak,
-                                       "traffic": None, "kernel": "k_trace_batch", "alg_bytes_per_ray": b_alg, "peak_source": peak_src}}))
+                                       "traffic": None, "kernel": "k_trace_batch", "alg_bytes_per_ray": b_alg, "peak_source": peak_src}})
     if dist is not None:
         dist.barrier(); dist.destroy_process_group()
 
@@ -368,12 +395,14 @@ def main():
     ap.add_argument("--rays", type=int, default=16 << 20, help="--workload raybatch: total rays")
     ap.add_argument("--bvh", default="sah", choices=["sah", "reference"])
     ap.add_argument("--megakernel", action="store_true")
+    ap.add_argument("--reduce", default="peer", choices=["peer", "nccl"], help="N > 1: how the rank films reach rank 0")
     ap.add_argument("--pipeline", default="fused", choices=["fused", "v1"], help="fused: camera paths traced in the trace pass, only hits are queued; v1: every ray queued")
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
+    quiet_stdout()
     if args.impl == "reference":
         run_reference(args)
     elif args.workload == "raybatch":

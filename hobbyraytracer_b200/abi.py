@@ -126,6 +126,11 @@ class Lib:
         self._sig("render_accumulate_device", i, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp], required=False)
         self._sig("film_resolve_device", i, [_vp, _vp, i, i, i, _vp, _vp, _vp, _vp], required=False)
         self._sig("film_bytes", i, [i, i], required=False)
+        self._sig("film_create", _vp, [i, i], required=False)
+        self._sig("film_destroy", None, [_vp], required=False)
+        self._sig("film_zero", i, [_vp, i, i, _vp], required=False)
+        self._sig("film_ipc_handle", i, [_vp, _vp], required=False)
+        self._sig("film_resolve_peers", i, [_vp, _vp, _vp, i, i, i, i, i, _vp, _vp, _vp, _vp], required=False)
         self._sig("get_stats", i, [_vp, C.POINTER(Stats)], required=False)
         self._sig("reset_stats", i, [_vp], required=False)
         # oracle-only

@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "hrt_shade.cuh"
@@ -66,6 +67,7 @@ struct hrt_scene {
     unsigned long long* d_counter = nullptr;                    // ray hand-out counter of k_trace_batch
     hrt_stats stats{};
     bool last_secondary_heavy = false;
+    std::vector<std::pair<cudaIpcMemHandle_t, void*>> peers;    // peer films opened through CUDA IPC (closed with the scene)
 };
 
 namespace {
@@ -265,6 +267,7 @@ void hrt_scene_destroy(hrt_scene* s)
         free_job(s); free_tb(s); free_scene_device(s);
         cudaFree(s->d_film); cudaFree(s->d_out); cudaFree(s->d_counter);
         if (s->h_ctl) cudaFreeHost(s->h_ctl);
+        for (auto& pr : s->peers) cudaIpcCloseMemHandle(pr.second);
         for (cudaEvent_t e : s->events) cudaEventDestroy(e);
         if (s->stream) cudaStreamDestroy(s->stream);
     }
@@ -403,6 +406,57 @@ int hrt_render(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, 
     if (out_sum) CK(cudaMemcpyAsync(out_sum, s->d_out, sizeof(float) * npix * 3, cudaMemcpyDeviceToHost, st));
     if (out_rgb8) CK(cudaMemcpyAsync(out_rgb8, d_rgb8, npix * 3, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    return 0;
+}
+
+void* hrt_film_create(int width, int height)
+{
+    const int bytes = hrt_film_bytes(width, height);
+    if (bytes < 0) return nullptr;
+    void* p = nullptr;
+    cudaError_t e = cudaSetDevice(g_device);
+    if (e == cudaSuccess) e = cudaMalloc(&p, (size_t)bytes);
+    if (e == cudaSuccess) e = cudaMemset(p, 0, (size_t)bytes);
+    if (e != cudaSuccess) { g_err = std::string("hrt_film_create: ") + cudaGetErrorString(e); if (p) cudaFree(p); return nullptr; }
+    return p;
+}
+void hrt_film_destroy(void* d_film) { if (d_film) cudaFree(d_film); }
+int hrt_film_zero(void* d_film, int width, int height, void* stream)
+{
+    const int bytes = hrt_film_bytes(width, height);
+    if (!d_film || bytes < 0) { g_err = "bad argument"; return HRT_ERR_ARG; }
+    CK(cudaMemsetAsync(d_film, 0, (size_t)bytes, (cudaStream_t)stream));
+    return 0;
+}
+int hrt_film_ipc_handle(void* d_film, void* out_handle)
+{
+    if (!d_film || !out_handle) { g_err = "NULL argument"; return HRT_ERR_ARG; }
+    static_assert(sizeof(cudaIpcMemHandle_t) == HRT_IPC_HANDLE_BYTES, "CUDA IPC handle size");
+    cudaIpcMemHandle_t h;
+    CK(cudaIpcGetMemHandle(&h, d_film));
+    memcpy(out_handle, &h, sizeof(h));
+    return 0;
+}
+int hrt_film_resolve_peers(hrt_scene* s, void* d_film, const void* peer_handles, int n_peers, int width, int height, int spp, int write_back,
+                           void* d_sum, void* d_mean, void* d_rgb8, void* stream)
+{
+    if (!s || !d_film || width < 1 || height < 1 || spp < 1 || n_peers < 0 || n_peers > HRT_MAX_PEERS || (n_peers > 0 && !peer_handles)) { g_err = "bad argument"; return HRT_ERR_ARG; }
+    CK(cudaSetDevice(s->device));
+    const long long* ptrs[HRT_MAX_PEERS];
+    for (int k = 0; k < n_peers; ++k) {
+        cudaIpcMemHandle_t h; memcpy(&h, (const char*)peer_handles + (size_t)k * HRT_IPC_HANDLE_BYTES, sizeof(h));
+        void* p = nullptr;
+        for (auto& pr : s->peers) if (memcmp(&pr.first, &h, sizeof(h)) == 0) p = pr.second;
+        if (!p) {
+            CK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+            s->peers.emplace_back(h, p);
+        }
+        ptrs[k] = (const long long*)p;
+    }
+    cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+    launch_film_resolve_peers((long long*)d_film, ptrs, n_peers, width * height, spp, write_back, (float*)d_sum, (float*)d_mean, (uint8_t*)d_rgb8,
+                              s->sm_count, st, &s->stats.launches);
     CK(cudaGetLastError());
     return 0;
 }

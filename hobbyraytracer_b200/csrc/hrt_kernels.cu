@@ -133,6 +133,32 @@ __global__ void __launch_bounds__(BLOCK) k_film_resolve(const long long* __restr
     }
 }
 
+// Reduce + resolve in one pass over NVLink peer memory: the films of the other ranks are mapped into this process
+// (CUDA IPC) and every pixel's four int64 lanes are pulled from each peer with two 128-bit loads, summed with the local
+// lanes and resolved on the spot — no staging buffer, no second pass over the 32 B/pixel film.  Integer sums: the image
+// is the same bit for bit as after an ncclSum reduce, whatever the number of ranks.
+struct PeerFilms { const long long* p[15]; int n; };
+__global__ void __launch_bounds__(BLOCK) k_film_resolve_peers(long long* __restrict__ film, PeerFilms peers, int npix, int spp, int write_back,
+                                                              float* __restrict__ sum, float* __restrict__ mean, uint8_t* __restrict__ rgb8)
+{
+    for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += gridDim.x * blockDim.x) {
+        const longlong2* mine = (const longlong2*)(film + (size_t)pix * FILM_LANES);
+        longlong2 a = mine[0], b = mine[1];
+        for (int k = 0; k < peers.n; ++k) {
+            const longlong2* q = (const longlong2*)(peers.p[k] + (size_t)pix * FILM_LANES);
+            const longlong2 c = q[0], d = q[1];                                // NVLink reads, 16 B each, coalesced across the warp
+            a.x += c.x; a.y += c.y; b.x += d.x; b.y += d.y;                     // lane 3 holds <= 7-bit counters per field: sums of <= 16 ranks cannot carry
+        }
+        long long px[4] = {a.x, a.y, b.x, b.y};
+        if (write_back) { longlong2* o = (longlong2*)(film + (size_t)pix * FILM_LANES); o[0] = a; o[1] = b; }
+        V3 c = v3(film_channel(px, 0), film_channel(px, 1), film_channel(px, 2));
+        if (sum) { sum[3 * (size_t)pix] = c.x; sum[3 * (size_t)pix + 1] = c.y; sum[3 * (size_t)pix + 2] = c.z; }
+        c = c / (float)spp;                                                     // main.cpp:126
+        if (mean) { mean[3 * (size_t)pix] = c.x; mean[3 * (size_t)pix + 1] = c.y; mean[3 * (size_t)pix + 2] = c.z; }
+        if (rgb8) tonemap_write(c, rgb8 + 3 * (size_t)pix);
+    }
+}
+
 // ---- camera paths ---------------------------------------------------------------------------------------------------------
 // Path index p -> (local sample, pixel).  When the film is a whole number of 8x4 pixel tiles, 32 consecutive paths are
 // one tile of one sample, so a warp of fresh camera rays is a small screen-space block; otherwise pixels go in row order.
@@ -613,6 +639,13 @@ void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count,
 void launch_render_mega(const DScene& s, const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches)
 {
     k_render_mega<<<grid_for((long long)j.npix * j.s_count, sm_count, 16), BLOCK, 0, st>>>(s, j, cam); *launches += 1;
+}
+void launch_film_resolve_peers(long long* d_film, const long long* const* peers, int n_peers, int npix, int spp, int write_back,
+                                float* d_sum, float* d_mean, uint8_t* d_rgb8, int sm_count, cudaStream_t st, uint64_t* launches)
+{
+    PeerFilms pf; pf.n = n_peers;
+    for (int k = 0; k < 15; ++k) pf.p[k] = k < n_peers ? peers[k] : nullptr;
+    k_film_resolve_peers<<<grid_for(npix, sm_count, 16), BLOCK, 0, st>>>(d_film, pf, npix, spp, write_back, d_sum, d_mean, d_rgb8); *launches += 1;
 }
 void launch_film_resolve(const long long* d_film, int npix, int spp, float* d_sum, float* d_mean, uint8_t* d_rgb8, int sm_count, cudaStream_t st, uint64_t* launches)
 {

@@ -66,6 +66,9 @@ void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count,
 void launch_render_mega(const DScene& s, const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches);
 
 // film -> per-pixel float sums (may be null) / mean (may be null) / 8-bit tonemapped image (may be null)
+// the same over the local film + up to 15 peer films mapped through CUDA IPC (NVLink loads inside the kernel)
+void launch_film_resolve_peers(long long* d_film, const long long* const* peers, int n_peers, int npix, int spp, int write_back,
+                                float* d_sum, float* d_mean, uint8_t* d_rgb8, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_film_resolve(const long long* d_film, int npix, int spp, float* d_sum, float* d_mean, uint8_t* d_rgb8, int sm_count, cudaStream_t st, uint64_t* launches);
 
 } // namespace hrt

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define HRT_ABI_VERSION 2
+#define HRT_ABI_VERSION 3
 
 /* ---- error codes --------------------------------------------------------------------------- */
 #define HRT_OK            0
@@ -198,6 +198,21 @@ int hrt_render_accumulate_device(hrt_scene* s, const hrt_camera* cam, const hrt_
                                  void* d_film, void* stream);
 int hrt_film_resolve_device(hrt_scene* s, const void* d_film, int width, int height, int spp,
                             void* d_sum_or_null, void* d_mean_or_null, void* d_rgb8_or_null, void* stream);
+
+/* Reduce + resolve over NVLink peer memory (one process per GPU).  Films that other processes can map are allocated by the
+ * library (hrt_film_create: a zeroed cudaMalloc allocation of hrt_film_bytes, addressable by a CUDA IPC handle).  Every rank
+ * renders into its own film and publishes hrt_film_ipc_handle; after a barrier the root calls hrt_film_resolve_peers with the
+ * handles of the OTHER ranks: one kernel pulls the peers' lanes over NVLink, adds them to the local film as integers (the
+ * same bits as an ncclSum reduce) and writes float sums / means / the 8-bit image; write_back != 0 also stores the reduced
+ * film.  The peers must not touch their films until the root's stream has finished (barrier after the call). */
+#define HRT_IPC_HANDLE_BYTES 64
+#define HRT_MAX_PEERS 15
+void* hrt_film_create(int width, int height);
+void  hrt_film_destroy(void* d_film);
+int   hrt_film_zero(void* d_film, int width, int height, void* stream);
+int   hrt_film_ipc_handle(void* d_film, void* out_handle);
+int   hrt_film_resolve_peers(hrt_scene* s, void* d_film, const void* peer_handles, int n_peers, int width, int height, int spp,
+                             int write_back, void* d_sum_or_null, void* d_mean_or_null, void* d_rgb8_or_null, void* stream);
 
 int hrt_get_stats(hrt_scene* s, hrt_stats* out);
 int hrt_reset_stats(hrt_scene* s);

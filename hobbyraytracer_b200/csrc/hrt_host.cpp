@@ -558,11 +558,18 @@ std::string flatten(HostScene& s, int bvh_mode, uint64_t seed)
         }
     }
     s.tlas_cull_scale = any_quat ? cull_scale : 0.0f;
-    s.tlas = FastBvh();
+    s.tlas = FastBvh(); s.has_bounds = false;
     if (fast && !s.objects.empty()) {
         // float(double) may round inwards by half an ulp: push the bounds one step outwards
         for (size_t k = 0; k < obmin.size(); ++k) { obmin[k] = std::nextafter(obmin[k], -std::numeric_limits<float>::infinity()); obmax[k] = std::nextafter(obmax[k], std::numeric_limits<float>::infinity()); }
         build_fast_bvh(obmin, obmax, s.tlas, 1);
+        s.has_bounds = true;
+        for (int a = 0; a < 3; ++a) { s.bounds_lo[a] = 3.0e38f; s.bounds_hi[a] = -3.0e38f; }
+        for (size_t k = 0; k < obmin.size(); ++k) {
+            const int a = (int)(k % 3);
+            s.bounds_lo[a] = std::min(s.bounds_lo[a], obmin[k]); s.bounds_hi[a] = std::max(s.bounds_hi[a], obmax[k]);
+            if (!(obmin[k] > -1.0e30f) || !(obmax[k] < 1.0e30f)) s.has_bounds = false;
+        }
     }
     return "";
 }

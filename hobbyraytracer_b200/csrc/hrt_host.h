@@ -82,6 +82,8 @@ struct HostScene {
     std::vector<int> mesh_shapes;    // DScene::meshes[i] is built from shapes[mesh_shapes[i]]
     FastBvh tlas;
     float tlas_cull_scale = 1.0f;
+    float bounds_lo[3] = {0, 0, 0}, bounds_hi[3] = {0, 0, 0};   // union of the world-list entries' padded bounds
+    bool has_bounds = false;         // false: some entry is unbounded (or reference-order scene)
     double build_ms_ref = 0, build_ms_fast = 0;
 };
 

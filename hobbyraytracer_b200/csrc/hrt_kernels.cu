@@ -407,6 +407,27 @@ __global__ void __launch_bounds__(BLOCK, HRT_DYN_MIN_BLOCKS) k_wave2_secondary(D
     }
 }
 
+// Camera rays start outside most scenes and the larger part of a frame never comes near an object: such a ray is settled by
+// one slab test against the union of the world-list entries' padded bounds (the boxes the top-level tree is built from),
+// before trace_fast spends three IEEE reciprocals and the entry set-up of a walk on it.  Approximate reciprocals, so the
+// interval is widened by far more than their error; anything unusual about the ray (tiny, huge or non-finite components)
+// answers "cannot tell" and takes the full trace.
+__device__ __forceinline__ bool camera_ray_clears_scene(const DScene& s, const Ray& r, float t_min)
+{
+    const float lo = 1.0e-18f, hi = 1.0e18f;
+    const float dx = fabsf(r.d.x), dy = fabsf(r.d.y), dz = fabsf(r.d.z);
+    if (!(dx > lo && dy > lo && dz > lo && dx < hi && dy < hi && dz < hi)) return false;
+    if (!(fabsf(r.o.x) < hi && fabsf(r.o.y) < hi && fabsf(r.o.z) < hi)) return false;
+    const float ix = __fdividef(1.0f, r.d.x), iy = __fdividef(1.0f, r.d.y), iz = __fdividef(1.0f, r.d.z);
+    const float ax = (s.bounds_lo[0] - r.o.x) * ix, bx = (s.bounds_hi[0] - r.o.x) * ix;
+    const float ay = (s.bounds_lo[1] - r.o.y) * iy, by = (s.bounds_hi[1] - r.o.y) * iy;
+    const float az = (s.bounds_lo[2] - r.o.z) * iz, bz = (s.bounds_hi[2] - r.o.z) * iz;
+    float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
+    float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+    tn -= fabsf(tn) * 1.0e-5f; tf += fabsf(tf) * 1.0e-5f;
+    return tn > tf || tf < fminf(t_min, 0.0f);
+}
+
 template <int MINB>
 __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j, DCamera cam, int q, int skip_secondary)
 {
@@ -467,7 +488,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j
             ++c_sl; --c_left;
         }
         Hit h; h.t = 0.0f; h.prim = HRT_MISS; h.obj = -1; h.flags = 0;
-        if (active) {
+        if (active && !(primary && s.has_bounds && camera_ray_clears_scene(s, r, j.t_min))) {
             RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + (int)((st >> 8) & 0x7fffffu)), j.rng_mode);
             h = s.fast ? trace_fast<false>(s, r, j.t_min, hrt_inf(), key, st & 0xffu, nullptr) : trace_ref(s, r, j.t_min, hrt_inf(), key, st & 0xffu);
             if (h.flags & (HIT_RESOLVED | HIT_FALLBACK)) atomicAdd((h.flags & HIT_FALLBACK) ? &c->fallbacks : &c->resolved, 1ull);

@@ -86,6 +86,8 @@ struct DScene {
     int fast;                   // 0: reference visiting order everywhere; 1: SAH BVHs + reference-order re-trace of ambiguous rays
     int refill_secondary;       // 1: secondary rays are traced by the per-lane-refill pass (scenes with meshes: long, uneven walks)
     float tlas_cull_scale;      // lower bound of (reported t) / (world t * |d|) over RotateQuat objects; 0 if none
+    int has_bounds;             // 1: bounds_lo/hi enclose every world-list entry (camera rays that pass outside are misses)
+    float bounds_lo[3], bounds_hi[3];
     int nan_obj;                // what world->hit returns for a ray whose origin is NaN in all components: every
     uint32_t nan_prim;          // primitive accepts it (all comparisons false), so the last one in reference order wins; -1: miss
 };

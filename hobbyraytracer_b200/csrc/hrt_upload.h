@@ -54,6 +54,8 @@ DScene make_dscene(HostScene& s, Up& up)
     d.fast = fast ? 1 : 0;
     d.refill_secondary = (fast && !meshes.empty()) ? 1 : 0;
     d.tlas_cull_scale = s.tlas_cull_scale;
+    d.has_bounds = (fast && s.has_bounds) ? 1 : 0;
+    for (int a = 0; a < 3; ++a) { d.bounds_lo[a] = s.bounds_lo[a]; d.bounds_hi[a] = s.bounds_hi[a]; }
     d.nan_obj = -1; d.nan_prim = HRT_MISS;
     for (int i = (int)s.d_objects.size() - 1; i >= 0 && d.nan_obj < 0; --i) {
         const DObject& ob = s.d_objects[(size_t)i];

@@ -28,6 +28,7 @@ import numpy as np  # noqa: E402
 from hobbyraytracer_b200 import abi, scenes  # noqa: E402
 
 CACHE = os.path.join(ROOT, "tests", "_cache")
+BVH_MODES = {"reference": 0, "sah": 1, "lbvh_gpu": 2, "lbvh_host": 3}      # abi.BVH_*
 ORACLE_SO = os.path.join(ROOT, "oracle", "_build", "liboracle.so")
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "libhrt_ref.so")
 
@@ -192,7 +193,7 @@ def run_own(args):
     lib.check(lib.fn("set_device")(local), "set_device")
     sd, cam, w, h, spp, info = make_workload(args.workload, args)
     c = scenes.camera_for(cam, w, h)
-    bvh = abi.BVH_SAH if args.bvh == "sah" else abi.BVH_REFERENCE
+    bvh = BVH_MODES[args.bvh]
     t0 = time.perf_counter(); sc = sd.build(lib, bvh, 3); t_commit = time.perf_counter() - t0
     npix = w * h
     film = multigpu.new_film(lib, w, h)
@@ -291,7 +292,7 @@ def run_own(args):
                            "cache": "camera paths are generated on the device every step (nothing to reuse); between steps the 66 MB film is re-zeroed and the 600 MB of queues rewritten, both larger than L2 with the 33 MB scene; no flush needed"},
                 "e2e": {"value": float(e2e_r.item()) / float(e2e_s.item()) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": scene_bytes,
                         "d2h_bytes_per_step": npix * 15, "steps": e2e_steps, "includes": "scene build + BVH build + upload, render, float film + 8-bit image read-back"},
-                "gpu_launches": int(launches), "commit_s": t_commit, "replayed_fraction": float(st.retraced) / max(float(st.rays), 1.0), "ref_walk_rays": int(st.prim_tests),
+                "gpu_launches": int(launches), "commit_s": t_commit, "build_ms": st.ms_build, "replayed_fraction": float(st.retraced) / max(float(st.rays), 1.0), "ref_walk_rays": int(st.prim_tests),
                 "kernel_ms": {"trace": st.ms_trace, "shade": st.ms_shade, "other": st.ms_other, "total": st.ms_total, "note": "rank 0, CUDA events inside the timed region"},
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": (ach / peak) if ach else None, "traffic": traffic,
                              "kernel": "k_wave_trace" if args.pipeline == "v1" else "k_wave2_trace", "alg_bytes_per_ray": b_alg, "trace_launches": int(st.launches) // 2, "peak_source": peak_src,
@@ -323,7 +324,7 @@ def run_raybatch(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lib = pkg.load(); lib.check(lib.fn("set_device")(local), "set_device")
     sd, cam, info = scenes.big_mesh_scene(CACHE, quads=args.quads, env_w=64, env_h=32)
-    t0 = time.perf_counter(); sc = sd.build(lib, abi.BVH_SAH, 3); t_commit = time.perf_counter() - t0
+    t0 = time.perf_counter(); sc = sd.build(lib, BVH_MODES[args.bvh], 3); t_commit = time.perf_counter() - t0
     n_total = args.rays; n = n_total // world
     rays_h = scenes.random_rays(n, (0, 1, 0), 1.2 * 1.5, seed=0xC0FFEE + rank)
     rays = torch.from_numpy(rays_h).cuda()
@@ -393,7 +394,8 @@ def main():
     ap.add_argument("--width", type=int, default=0); ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--quads", type=int, default=2290)
     ap.add_argument("--rays", type=int, default=16 << 20, help="--workload raybatch: total rays")
-    ap.add_argument("--bvh", default="sah", choices=["sah", "reference"])
+    ap.add_argument("--bvh", default="sah", choices=["sah", "reference", "lbvh_gpu", "lbvh_host"],
+                    help="sah: host binned-SAH trees; lbvh_gpu: the whole per-mesh build on the device (Morton LBVH); lbvh_host: its host mirror")
     ap.add_argument("--megakernel", action="store_true")
     ap.add_argument("--reduce", default="peer", choices=["peer", "nccl"], help="N > 1: how the rank films reach rank 0")
     ap.add_argument("--pipeline", default="fused", choices=["fused", "v1"], help="fused: camera paths traced in the trace pass, only hits are queued; v1: every ray queued")

@@ -19,7 +19,7 @@ MISS = 0xFFFFFFFF
 
 MAT_LAMBERTIAN, MAT_METAL, MAT_DIELECTRIC, MAT_ISOTROPIC, MAT_DIFFUSE_LIGHT, MAT_PBR, MAT_UVTEST = range(7)
 XF_TRANSLATE, XF_SCALE, XF_ROTATE_QUAT, XF_ROTATE_Y, XF_ROTATE_EULER_DEG, XF_ROTATE_Y_DEG = range(6)
-BVH_REFERENCE, BVH_SAH, BVH_LBVH_GPU = range(3)
+BVH_REFERENCE, BVH_SAH, BVH_LBVH_GPU, BVH_LBVH_HOST = range(4)
 RENDER_MEGAKERNEL = 1
 RENDER_WAVEFRONT_V1 = 2
 
@@ -142,6 +142,7 @@ class Lib:
         self._sig("scatter_batch", i, [_vp, i, _vp, _vp, i64, u64, _vp], required=False)
         self._sig("texture_eval", i, [_vp, i, _vp, i64, _vp], required=False)
         self._sig("mesh_bvh_nodes", i64, [_vp, i, _vp, _vp], required=False)
+        self._sig("scene_mesh_array", i64, [_vp, i, i, _vp, i64], required=False)
         self._sig("hardware_threads", i, [], required=False)
 
     def check(self, rc: int, what: str = "") -> int:
@@ -314,6 +315,17 @@ class Scene:
         b = np.empty((height, width, 3), np.uint8) if want_rgb8 else None
         self.lib.check(self.lib.fn("render")(self.h, C.byref(cam), C.byref(p), _ptr(s), _ptr(b)), "render")
         return s, b
+
+    def mesh_array(self, mesh_index: int, which: int) -> np.ndarray:
+        """One per-mesh array of the committed scene as float32 words (hrt_scene_mesh_array): 0 reference-topology nodes,
+        1 fast-tree nodes, 2 leaf records, 3 triangle positions, 4 triangle attributes."""
+        f = self.lib.fn("scene_mesh_array")
+        n = f(self.h, mesh_index, which, None, 0)
+        self.lib.check(n, "scene_mesh_array")
+        out = np.empty(n // 4, np.float32)
+        if n:
+            self.lib.check(f(self.h, mesh_index, which, _ptr(out), n), "scene_mesh_array")
+        return out
 
     def stats(self) -> Stats:
         st = Stats(); self.lib.check(self.lib.fn("get_stats")(self.h, C.byref(st)), "get_stats"); return st

@@ -8,10 +8,12 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <utility>
 #include <vector>
 
 #include "hrt_shade.cuh"
+#include "hrt_bvh_gpu.h"
 #include "hrt_kernels.h"
 #include "hrt_upload.h"
 
@@ -67,6 +69,8 @@ struct hrt_scene {
     unsigned long long* d_counter = nullptr;                    // ray hand-out counter of k_trace_batch
     hrt_stats stats{};
     bool last_secondary_heavy = false;
+    double ms_build_gpu = 0; int bvh_fallbacks = 0;             // HRT_BVH_LBVH_GPU: upload + device build time, meshes handed back to the host builder
+    std::vector<DMesh> meshes_view;                             // host copy of DScene::meshes (hrt_scene_mesh_array)
     std::vector<std::pair<cudaIpcMemHandle_t, void*>> peers;    // peer films opened through CUDA IPC (closed with the scene)
 };
 
@@ -297,22 +301,60 @@ int64_t hrt_scene_prim_count(const hrt_scene* s) { if (!s) { g_err = "scene is N
 int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed)
 {
     NEED(s);
-    if (bvh_mode < HRT_BVH_REFERENCE || bvh_mode > HRT_BVH_LBVH_GPU) { g_err = "unknown bvh mode"; return HRT_ERR_ARG; }
-    if (bvh_mode == HRT_BVH_LBVH_GPU) bvh_mode = HRT_BVH_SAH;     // the GPU builder is not implemented yet: host SAH, same node format
+    if (bvh_mode < HRT_BVH_REFERENCE || bvh_mode > HRT_BVH_LBVH_HOST) { g_err = "unknown bvh mode"; return HRT_ERR_ARG; }
     CK(cudaSetDevice(s->device));
     cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, s->device));
     s->sm_count = prop.multiProcessorCount;
     std::string e = flatten(s->host, bvh_mode, seed);
     if (!e.empty()) { g_err = e; return HRT_ERR_ARG; }
     CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    s->ms_build_gpu = 0; s->bvh_fallbacks = 0;
+    size_t dev_bytes = 0;
+    for (int shape : s->host.mesh_shapes) {                       // HRT_BVH_LBVH_GPU: per-mesh arrays are built on the device
+        HostShape& sh = s->host.shapes[(size_t)shape];
+        if (!sh.gpu_pending) continue;
+        GpuMeshBuild b; std::string berr;
+        if (!build_mesh_gpu(sh.pos.data(), sh.nrm.data(), sh.uv.data(), sh.n_tri, seed, shape, s->stream, s->scene_allocs, dev_bytes, b, berr, &s->stats.launches)) {
+            g_err = "device BVH build failed: " + berr; free_scene_device(s); return HRT_ERR_CUDA;
+        }
+        sh.gpu_pending = false;
+        if (b.fallback) {                                         // (non-finite positions, degenerate Morton order): the host builder's SAH tree
+            int nt = (int)std::thread::hardware_concurrency(); if (nt < 1) nt = 1;
+            build_mesh_host(sh, HRT_BVH_SAH, seed, shape, nt, s->host.build_ms_ref, s->host.build_ms_fast);
+            ++s->bvh_fallbacks;
+            continue;
+        }
+        sh.has_dev = true; sh.dev = b.mesh;
+        sh.n_ref_nodes = b.n_ref_nodes; sh.n_fast_nodes = b.n_fast_nodes; sh.n_leaves = b.n_leaves; sh.last_tri_r = b.last_tri_r;
+        sh.fast.depth = b.depth;
+        s->ms_build_gpu += b.ms_upload + b.ms_build;
+    }
     DevUp up(s->scene_allocs);
     s->d = make_dscene(s->host, up);
     if (const char* e = getenv("HRT_REFILL_SECONDARY")) s->d.refill_secondary = (atoi(e) != 0 && s->d.fast) ? 1 : 0;   // A/B override
     if (up.failed) { g_err = "scene upload failed: " + up.msg; free_scene_device(s); return HRT_ERR_CUDA; }
-    s->scene_bytes = up.bytes;
+    s->scene_bytes = up.bytes + dev_bytes;
+    s->meshes_view.resize(s->host.mesh_shapes.size());
+    if (!s->meshes_view.empty()) CK(cudaMemcpy(s->meshes_view.data(), s->d.meshes, s->meshes_view.size() * sizeof(DMesh), cudaMemcpyDeviceToHost));
     CK(cudaDeviceSynchronize());
     s->host.committed = true;
     return 0;
+}
+
+int64_t hrt_scene_mesh_array(hrt_scene* s, int mesh_index, int which, void* out, int64_t capacity_bytes)
+{
+    if (!s || !s->host.committed) { g_err = "scene not committed"; return HRT_ERR_STATE; }
+    if (mesh_index < 0 || (size_t)mesh_index >= s->meshes_view.size() || which < 0 || which > 4) { g_err = "bad argument"; return HRT_ERR_ARG; }
+    const HostShape& sh = s->host.shapes[(size_t)s->host.mesh_shapes[(size_t)mesh_index]];
+    const DMesh& m = s->meshes_view[(size_t)mesh_index];
+    const void* src[5] = {m.ref_nodes, m.fast_nodes, m.fast_leaves, m.tris, m.attrs};
+    const size_t bytes[5] = {sh.n_ref_nodes * 32, sh.n_fast_nodes * 64, sh.n_leaves * 128, (size_t)sh.n_tri * 48, (size_t)sh.n_tri * 64};
+    if (out) {
+        if (capacity_bytes < (int64_t)bytes[which]) { g_err = "buffer too small"; return HRT_ERR_ARG; }
+        CK(cudaSetDevice(s->device));
+        if (bytes[which]) CK(cudaMemcpy(out, src[which], bytes[which], cudaMemcpyDeviceToHost));
+    }
+    return (int64_t)bytes[which];
 }
 
 int hrt_trace_batch_device(hrt_scene* s, const void* d_rays, int64_t n, void* d_prim_id, void* d_t, uint64_t rng_seed, void* stream)
@@ -464,7 +506,7 @@ int hrt_film_resolve_peers(hrt_scene* s, void* d_film, const void* peer_handles,
 int hrt_get_stats(hrt_scene* s, hrt_stats* out)
 {
     if (!s || !out) { g_err = "NULL argument"; return HRT_ERR_ARG; }
-    *out = s->stats; out->scene_bytes = s->scene_bytes; out->ms_build = s->host.build_ms_ref + s->host.build_ms_fast;
+    *out = s->stats; out->scene_bytes = s->scene_bytes; out->ms_build = s->host.build_ms_ref + s->host.build_ms_fast + s->ms_build_gpu;
     return 0;
 }
 int hrt_reset_stats(hrt_scene* s)

@@ -1,0 +1,29 @@
+// hrt_bvh_gpu.h — interface of the device-side mesh builder (hrt_bvh_gpu.cu) used by hrt_scene_commit(HRT_BVH_LBVH_GPU).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "hrt_types.h"
+
+namespace hrt {
+
+struct GpuMeshBuild {
+    DMesh mesh{};                    // device pointers + roots (prim_base / material are filled in by the caller)
+    size_t n_ref_nodes = 0, n_fast_nodes = 0, n_leaves = 0;
+    int last_tri_r = -1;             // right triangle of the last bottom node (what a NaN-origin ray reports, hrt_upload.h)
+    int depth = 0;                   // depth of the fast tree
+    bool fallback = false;           // true: this mesh cannot be built here (why), the host builder takes over
+    std::string why;
+    double ms_upload = 0, ms_build = 0;
+};
+
+// Uploads the raw triangle soup (9 + 9 + 6 floats per triangle, the layout of hrt_scene_add_mesh) and builds every
+// per-mesh array on the device.  Result allocations are appended to `allocs` (owned by the scene).  Returns false with
+// `err` set on a CUDA failure.
+bool build_mesh_gpu(const float* pos, const float* nrm, const float* uv, int64_t n_tri, uint64_t seed, int shape_id,
+                    cudaStream_t st, std::vector<void*>& allocs, size_t& bytes, GpuMeshBuild& out, std::string& err, uint64_t* launches);
+
+} // namespace hrt

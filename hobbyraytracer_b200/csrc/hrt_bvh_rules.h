@@ -38,7 +38,7 @@ inline void tree_shape_fill(TreeShape& ts, uint32_t n)
 {
     ts.n = n; ts.levels = 0;
     int L = 0;
-    for (; L < TREE_MAX_LEVELS; ++L) { ts.lo[L] = n >> L; if ((n >> L) + 1 <= 2 || (((n >> L) << L) == n && (n >> L) <= 2)) { ++L; break; } }
+    for (; L < TREE_MAX_LEVELS; ++L) { ts.lo[L] = n >> L; if ((n >> L) <= 1) { ++L; break; } }   // the last level only has ranges of <= 2
     ts.levels = L;
     for (int l = L - 1; l >= 0; --l)
         for (int k = 0; k < 2; ++k) {

@@ -7,6 +7,7 @@
 // boxes triangle.cpp:133-151, the camera basis camera.h:9-30) is done here on the host too, in fp32, in the
 // reference's evaluation order (build with -ffp-contract=off).
 #include "hrt_host.h"
+#include "hrt_bvh_rules.h"
 
 #include <algorithm>
 #include <chrono>
@@ -142,6 +143,7 @@ struct RefBuilder {
     const std::vector<float>& bmin; const std::vector<float>& bmax;
     std::vector<float4>& nodes; std::vector<int>& order;
     std::map<size_t, uint64_t> count;
+    bool stable = false;
     uint64_t n_nodes(size_t n)
     {
         if (n <= 2) return 1;
@@ -167,7 +169,8 @@ struct RefBuilder {
             if (key(order[start]) < key(order[start + 1])) { left = ~order[start]; right = ~order[start + 1]; }
             else { left = ~order[start + 1]; right = ~order[start]; }
         } else {
-            std::sort(order.begin() + start, order.begin() + end, [&](int a, int b) { return key(a) < key(b); });
+            if (stable) std::stable_sort(order.begin() + start, order.begin() + end, [&](int a, int b) { return key(a) < key(b); });
+            else std::sort(order.begin() + start, order.begin() + end, [&](int a, int b) { return key(a) < key(b); });
             size_t mid = start + n / 2;
             uint64_t nl = n_nodes_ro(mid - start);
             left = self + 1; right = self + 1 + (int)nl;
@@ -192,14 +195,14 @@ struct RefBuilder {
 };
 } // namespace
 
-void build_ref_bvh(HostShape& sh, uint64_t seed, int shape_id, int n_threads)
+void build_ref_bvh(HostShape& sh, uint64_t seed, int shape_id, int n_threads, bool stable)
 {
     sh.ref.nodes.clear(); sh.ref.root = -1;
     if (sh.n_tri == 0) return;
     std::vector<float> bmin, bmax; triangle_boxes(sh, bmin, bmax);
     std::vector<int> order((size_t)sh.n_tri);
     for (int64_t i = 0; i < sh.n_tri; ++i) order[(size_t)i] = (int)i;
-    RefBuilder b{bmin, bmax, sh.ref.nodes, order, {}};
+    RefBuilder b{bmin, bmax, sh.ref.nodes, order, {}, stable};
     uint64_t total = b.n_nodes((size_t)sh.n_tri);
     sh.ref.nodes.resize((size_t)total * 2);
     Lcg rng; rng.s = mix64(seed ^ mix64((uint64_t)shape_id));
@@ -336,6 +339,81 @@ void build_fast_bvh(const std::vector<float>& bmin, const std::vector<float>& bm
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// Host mirror of the device LBVH (hrt_bvh_gpu.cu: k_centre_bounds, k_morton, sort, k_karras, k_refit) — same rules
+// (hrt_bvh_rules.h), same node numbering (internal node i of the hierarchy is node i), boxes united child 0 first.
+// ------------------------------------------------------------------------------------------------------------
+namespace {
+inline uint32_t f2u(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+inline float u2f(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
+inline float key_to_float(uint32_t k) { return u2f((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k); }
+}
+
+void build_lbvh_host(const std::vector<float>& bmin, const std::vector<float>& bmax, FastBvh& out)
+{
+    const int64_t n = (int64_t)(bmin.size() / 3);
+    out.nodes.clear(); out.order.clear(); out.root = -1; out.depth = 0;
+    if (n == 0) return;
+    if (n == 1) { out.root = ~0; return; }
+    uint32_t lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u};
+    for (int64_t i = 0; i < n; ++i)
+        for (int a = 0; a < 3; ++a) {
+            uint32_t k = rule_float_key(f2u(rule_centre(bmin[(size_t)i * 3 + a], bmax[(size_t)i * 3 + a])));
+            lo[a] = std::min(lo[a], k); hi[a] = std::max(hi[a], k);
+        }
+    std::vector<uint64_t> code((size_t)n);
+    for (int64_t i = 0; i < n; ++i) {
+        uint32_t cell[3];
+        for (int a = 0; a < 3; ++a) {
+            const float l = key_to_float(lo[a]), h = key_to_float(hi[a]);
+            cell[a] = rule_cell(rule_centre(bmin[(size_t)i * 3 + a], bmax[(size_t)i * 3 + a]), l, rule_scale(l, h));
+        }
+        code[(size_t)i] = rule_morton(cell[0], cell[1], cell[2]);
+    }
+    std::vector<int> order((size_t)n);
+    for (int64_t i = 0; i < n; ++i) order[(size_t)i] = (int)i;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return code[(size_t)a] < code[(size_t)b]; });
+    std::vector<uint64_t> sorted((size_t)n);
+    for (int64_t i = 0; i < n; ++i) sorted[(size_t)i] = code[(size_t)order[(size_t)i]];
+    out.nodes.assign((size_t)(n - 1) * 4, float4{0, 0, 0, 0});
+    std::vector<int> lc((size_t)n - 1), rc((size_t)n - 1);
+    for (int64_t i = 0; i < n - 1; ++i) {
+        int64_t first, last, split;
+        rule_karras(sorted.data(), n, i, first, last, split);
+        lc[(size_t)i] = (split == first) ? ~order[(size_t)split] : (int)split;
+        rc[(size_t)i] = (split + 1 == last) ? ~order[(size_t)split + 1] : (int)(split + 1);
+    }
+    // boxes bottom-up (explicit stack: the hierarchy can be ~100 levels deep on degenerate input)
+    std::vector<Box3> nb((size_t)n - 1); std::vector<int> nd((size_t)n - 1, 0);
+    std::vector<std::pair<int, int>> stack; stack.push_back({0, 0});
+    auto child_box = [&](int c, Box3& b, int& d) {
+        if (c < 0) { size_t it = (size_t)(~c); for (int a = 0; a < 3; ++a) { b.mn[a] = bmin[it * 3 + a]; b.mx[a] = bmax[it * 3 + a]; } d = 0; }
+        else { b = nb[(size_t)c]; d = nd[(size_t)c]; }
+    };
+    while (!stack.empty()) {
+        auto [node, stage] = stack.back();
+        if (stage == 0) {
+            stack.back().second = 1;
+            if (rc[(size_t)node] >= 0) stack.push_back({rc[(size_t)node], 0});
+            if (lc[(size_t)node] >= 0) stack.push_back({lc[(size_t)node], 0});
+            continue;
+        }
+        stack.pop_back();
+        Box3 lb, rb; int dl, dr;
+        child_box(lc[(size_t)node], lb, dl); child_box(rc[(size_t)node], rb, dr);
+        float4 n0, n1, n2, n3;
+        n0.x = lb.mn[0]; n0.y = lb.mx[0]; n0.z = lb.mn[1]; n0.w = lb.mx[1];
+        n1.x = rb.mn[0]; n1.y = rb.mx[0]; n1.z = rb.mn[1]; n1.w = rb.mx[1];
+        n2.x = lb.mn[2]; n2.y = lb.mx[2]; n2.z = rb.mn[2]; n2.w = rb.mx[2];
+        std::memcpy(&n3.x, &lc[(size_t)node], 4); std::memcpy(&n3.y, &rc[(size_t)node], 4); n3.z = 0; n3.w = 0;
+        float4* N = &out.nodes[(size_t)node * 4]; N[0] = n0; N[1] = n1; N[2] = n2; N[3] = n3;
+        Box3 u;
+        for (int a = 0; a < 3; ++a) { u.mn[a] = cmin(lb.mn[a], rb.mn[a]); u.mx[a] = cmax(lb.mx[a], rb.mx[a]); }
+        nb[(size_t)node] = u; nd[(size_t)node] = std::max(dl, dr) + 1;
+    }
+    out.root = 0; out.depth = nd[0]; out.order = std::move(order);
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // Exact repack of a decoded Radiance image (texture.cpp:99-115 -> stb_image stbi__hdr_convert: byte * 2^(e-136))
 // into one 32-bit word per texel; refuses (returns false) unless every texel round-trips bit for bit.
 // ------------------------------------------------------------------------------------------------------------
@@ -464,6 +542,53 @@ DBox world_bounds(const HostShape& sh, const HostObject& o)
 
 } // namespace
 
+void build_mesh_host(HostShape& sh, int bvh_mode, uint64_t seed, int shape_id, int nt, double& ms_ref, double& ms_fast)
+{
+    const bool fast = bvh_mode != HRT_BVH_REFERENCE;
+    const bool lbvh = bvh_mode == HRT_BVH_LBVH_HOST || bvh_mode == HRT_BVH_LBVH_GPU;
+    double t0 = now_ms();
+    build_ref_bvh(sh, seed, shape_id, nt, lbvh);
+    ms_ref += now_ms() - t0;
+    size_t n = (size_t)sh.n_tri;
+    sh.tris4.resize(n * 3); sh.attrs4.resize(n * 4);
+    for (size_t i = 0; i < n; ++i) {
+        const float* P = &sh.pos[i * 9]; const float* N = &sh.nrm[i * 9]; const float* T = &sh.uv[i * 6];
+        for (int v = 0; v < 3; ++v) { float4 q; q.x = P[v * 3]; q.y = P[v * 3 + 1]; q.z = P[v * 3 + 2]; q.w = 0; sh.tris4[i * 3 + v] = q; }
+        float4 a0, a1, a2, a3;
+        a0.x = N[0]; a0.y = N[1]; a0.z = N[2]; a0.w = T[0];
+        a1.x = N[3]; a1.y = N[4]; a1.z = N[5]; a1.w = T[1];
+        a2.x = N[6]; a2.y = N[7]; a2.z = N[8]; a2.w = T[2];
+        a3.x = T[3]; a3.y = T[4]; a3.z = T[5]; a3.w = 0;
+        sh.attrs4[i * 4] = a0; sh.attrs4[i * 4 + 1] = a1; sh.attrs4[i * 4 + 2] = a2; sh.attrs4[i * 4 + 3] = a3;
+    }
+    sh.leaves.clear(); sh.fast = FastBvh(); sh.last_tri_r = -1;
+    if (fast && sh.ref.root >= 0) {
+        t0 = now_ms();
+        size_t n_nodes = sh.ref.nodes.size() / 2;
+        std::vector<float> bmin, bmax;
+        for (size_t k = 0; k < n_nodes; ++k) {
+            const float4& a = sh.ref.nodes[k * 2]; const float4& b = sh.ref.nodes[k * 2 + 1];
+            int left, right; std::memcpy(&left, &a.w, 4); std::memcpy(&right, &b.w, 4);
+            if (left >= 0) continue;                                     // not a bottom node
+            bmin.push_back(a.x); bmin.push_back(a.y); bmin.push_back(a.z);
+            bmax.push_back(b.x); bmax.push_back(b.y); bmax.push_back(b.z);
+            size_t tl = (size_t)(~left), tr = (size_t)(~right);
+            float4 rec[8];
+            rec[0] = a; rec[1] = b;
+            int il = (int)tl, ir = (int)tr; std::memcpy(&rec[0].w, &il, 4); std::memcpy(&rec[1].w, &ir, 4);
+            for (int v = 0; v < 3; ++v) { rec[2 + v] = sh.tris4[tl * 3 + v]; rec[5 + v] = sh.tris4[tr * 3 + v]; }
+            sh.leaves.insert(sh.leaves.end(), rec, rec + 8);
+            sh.last_tri_r = ir;
+        }
+        if (lbvh) {
+            build_lbvh_host(bmin, bmax, sh.fast);
+            if (sh.fast.depth > FAST_MAX_DEPTH) build_fast_bvh(bmin, bmax, sh.fast, nt);   // same decision as the device builder's fallback
+        } else build_fast_bvh(bmin, bmax, sh.fast, nt);
+        ms_fast += now_ms() - t0;
+    }
+    sh.n_ref_nodes = sh.ref.nodes.size() / 2; sh.n_fast_nodes = sh.fast.nodes.size() / 4; sh.n_leaves = sh.leaves.size() / 8;
+}
+
 std::string flatten(HostScene& s, int bvh_mode, uint64_t seed)
 {
     const bool fast = bvh_mode != HRT_BVH_REFERENCE;
@@ -480,42 +605,9 @@ std::string flatten(HostScene& s, int bvh_mode, uint64_t seed)
         if (sh.kind != SHAPE_MESH || sh.used) { sh.used = true; continue; }
         sh.used = true;
         sh.mesh_index = (int)s.mesh_shapes.size(); s.mesh_shapes.push_back(o.shape);
-        double t0 = now_ms();
-        build_ref_bvh(sh, seed, o.shape, nt);
-        s.build_ms_ref += now_ms() - t0;
-        size_t n = (size_t)sh.n_tri;
-        sh.tris4.resize(n * 3); sh.attrs4.resize(n * 4);
-        for (size_t i = 0; i < n; ++i) {
-            const float* P = &sh.pos[i * 9]; const float* N = &sh.nrm[i * 9]; const float* T = &sh.uv[i * 6];
-            for (int v = 0; v < 3; ++v) { float4 q; q.x = P[v * 3]; q.y = P[v * 3 + 1]; q.z = P[v * 3 + 2]; q.w = 0; sh.tris4[i * 3 + v] = q; }
-            float4 a0, a1, a2, a3;
-            a0.x = N[0]; a0.y = N[1]; a0.z = N[2]; a0.w = T[0];
-            a1.x = N[3]; a1.y = N[4]; a1.z = N[5]; a1.w = T[1];
-            a2.x = N[6]; a2.y = N[7]; a2.z = N[8]; a2.w = T[2];
-            a3.x = T[3]; a3.y = T[4]; a3.z = T[5]; a3.w = 0;
-            sh.attrs4[i * 4] = a0; sh.attrs4[i * 4 + 1] = a1; sh.attrs4[i * 4 + 2] = a2; sh.attrs4[i * 4 + 3] = a3;
-        }
-        sh.leaves.clear(); sh.fast = FastBvh();
-        if (fast && sh.ref.root >= 0) {
-            t0 = now_ms();
-            size_t n_nodes = sh.ref.nodes.size() / 2;
-            std::vector<float> bmin, bmax;
-            for (size_t k = 0; k < n_nodes; ++k) {
-                const float4& a = sh.ref.nodes[k * 2]; const float4& b = sh.ref.nodes[k * 2 + 1];
-                int left, right; std::memcpy(&left, &a.w, 4); std::memcpy(&right, &b.w, 4);
-                if (left >= 0) continue;                                     // not a bottom node
-                bmin.push_back(a.x); bmin.push_back(a.y); bmin.push_back(a.z);
-                bmax.push_back(b.x); bmax.push_back(b.y); bmax.push_back(b.z);
-                size_t tl = (size_t)(~left), tr = (size_t)(~right);
-                float4 rec[8];
-                rec[0] = a; rec[1] = b;
-                int il = (int)tl, ir = (int)tr; std::memcpy(&rec[0].w, &il, 4); std::memcpy(&rec[1].w, &ir, 4);
-                for (int v = 0; v < 3; ++v) { rec[2 + v] = sh.tris4[tl * 3 + v]; rec[5 + v] = sh.tris4[tr * 3 + v]; }
-                sh.leaves.insert(sh.leaves.end(), rec, rec + 8);
-            }
-            build_fast_bvh(bmin, bmax, sh.fast, nt);
-            s.build_ms_fast += now_ms() - t0;
-        }
+        sh.gpu_pending = sh.has_dev = false;
+        if (bvh_mode == HRT_BVH_LBVH_GPU && sh.n_tri > 0) { sh.gpu_pending = true; continue; }   // built on the device by hrt_scene_commit
+        build_mesh_host(sh, bvh_mode, seed, o.shape, nt, s.build_ms_ref, s.build_ms_fast);
     }
 
     // world list

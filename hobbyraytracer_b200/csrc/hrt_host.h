@@ -55,6 +55,12 @@ struct HostShape {
     FastBvh fast;
     std::vector<float4> tris4, attrs4;   // device layouts of hrt_types.h (DMesh::tris, DMesh::attrs)
     std::vector<float4> leaves;          // DMesh::fast_leaves
+    // HRT_BVH_LBVH_GPU: flatten() leaves the mesh to the device builder (gpu_pending); hrt_scene_commit then stores the
+    // device-built view here (has_dev) and make_dscene hands it out instead of uploading host arrays
+    bool gpu_pending = false, has_dev = false;
+    DMesh dev{};
+    size_t n_ref_nodes = 0, n_fast_nodes = 0, n_leaves = 0;   // element counts behind the DMesh pointers (either builder)
+    int last_tri_r = -1;                 // right triangle of the last bottom node, -1: empty mesh
 };
 
 struct HostObject {
@@ -92,7 +98,13 @@ struct HostScene {
 DXform make_xform(const hrt_xform& x);
 
 // bvh.cpp:6-61: median split of box.min[axis] with axis = glm::linearRand(0,2) on the stream (seed, shape_id).
-void build_ref_bvh(HostShape& sh, uint64_t seed, int shape_id, int n_threads);
+// stable = false: ranges ordered with std::sort like bvh.cpp:39 (equal keys permute as libstdc++'s introsort does);
+// stable = true: equal keys keep their order, the rule of the GPU builder (hrt_bvh_rules.h).
+void build_ref_bvh(HostShape& sh, uint64_t seed, int shape_id, int n_threads, bool stable = false);
+// Morton LBVH over arbitrary boxes by the rules of hrt_bvh_rules.h: the host mirror of hrt_bvh_gpu.cu.
+void build_lbvh_host(const std::vector<float>& bmin, const std::vector<float>& bmax, FastBvh& out);
+// Per-mesh part of flatten() on the host: reference topology, device layouts, leaf records, fast tree.
+void build_mesh_host(HostShape& sh, int bvh_mode, uint64_t seed, int shape_id, int n_threads, double& ms_ref, double& ms_fast);
 // Binned-SAH BVH2 over arbitrary boxes (used for meshes and for the top-level BVH).
 void build_fast_bvh(const std::vector<float>& bmin, const std::vector<float>& bmax, FastBvh& out, int n_threads);
 void triangle_boxes(const HostShape& sh, std::vector<float>& bmin, std::vector<float>& bmax);   // triangle.cpp:133-151

@@ -18,6 +18,7 @@ DScene make_dscene(HostScene& s, Up& up)
     for (size_t i = 0; i < s.mesh_shapes.size(); ++i) {
         HostShape& sh = s.shapes[(size_t)s.mesh_shapes[i]];
         DMesh m{};
+        if (sh.has_dev) { m = sh.dev; m.prim_base = (uint32_t)sh.prim_base; m.material = sh.material; meshes[i] = m; continue; }
         m.ref_nodes = (const float4*)up.put(sh.ref.nodes.data(), sh.ref.nodes.size() * sizeof(float4));
         m.tris = (const float4*)up.put(sh.tris4.data(), sh.tris4.size() * sizeof(float4));
         m.attrs = (const float4*)up.put(sh.attrs4.data(), sh.attrs4.size() * sizeof(float4));
@@ -64,8 +65,8 @@ DScene make_dscene(HostScene& s, Up& up)
         else if (ob.kind != SHAPE_MESH) { d.nan_obj = i; d.nan_prim = ob.prim_base; }
         if (ob.kind == SHAPE_MESH) {                                             // last triangle of the left-then-right walk (bvh.cpp:69-78)
             const HostShape& sh = s.shapes[(size_t)s.mesh_shapes[(size_t)ob.mesh]];
-            if (sh.ref.root < 0 || sh.leaves.empty()) { d.nan_obj = -1; d.nan_prim = HRT_MISS; continue; }
-            if (!ob.medium) { int tr; std::memcpy(&tr, &sh.leaves[sh.leaves.size() - 7].w, 4); d.nan_obj = i; d.nan_prim = ob.prim_base + (uint32_t)tr; }
+            if (sh.n_leaves == 0 || sh.last_tri_r < 0) { d.nan_obj = -1; d.nan_prim = HRT_MISS; continue; }
+            if (!ob.medium) { d.nan_obj = i; d.nan_prim = ob.prim_base + (uint32_t)sh.last_tri_r; }
         }
     }
     return d;

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define HRT_ABI_VERSION 3
+#define HRT_ABI_VERSION 4
 
 /* ---- error codes --------------------------------------------------------------------------- */
 #define HRT_OK            0
@@ -95,7 +95,11 @@ enum {
                                flat world list, fixed left-then-right order: reproduces the reference's
                                visiting order, hence its tie-breaking, exactly                      */
     HRT_BVH_SAH       = 1,  /* binned-SAH BVH over each mesh + top-level BVH over world objects, built on host */
-    HRT_BVH_LBVH_GPU  = 2   /* Morton-code LBVH built on the GPU (same node format as SAH)          */
+    HRT_BVH_LBVH_GPU  = 2,  /* the whole per-mesh build on the GPU: triangle packing, the bvh.cpp:6-61 topology (one
+                               stable radix sort per level; equal keys keep their order where std::sort's introsort
+                               permutes them - identical whenever keys differ), leaf records and a Morton-code LBVH
+                               over them in the SAH node format; top-level BVH on the host                  */
+    HRT_BVH_LBVH_HOST = 3   /* host mirror of HRT_BVH_LBVH_GPU: same rules, arrays bit-identical (validation) */
 };
 
 typedef struct hrt_render_params {
@@ -126,7 +130,7 @@ typedef struct hrt_stats {
     uint64_t retraced;        /* rays whose answer depended on the visiting order and was settled by replaying the
                                  reference's sequential process over the collected candidates (HRT_BVH_SAH only) */
     uint64_t scene_bytes;     /* bytes of scene data resident in device memory after hrt_scene_commit  */
-    double   ms_build;        /* host time of the BVH builds in hrt_scene_commit                       */
+    double   ms_build;        /* time of the BVH builds in hrt_scene_commit (host builders, or upload + device build)   */
 } hrt_stats;
 
 typedef struct hrt_scene hrt_scene;
@@ -213,6 +217,11 @@ int   hrt_film_zero(void* d_film, int width, int height, void* stream);
 int   hrt_film_ipc_handle(void* d_film, void* out_handle);
 int   hrt_film_resolve_peers(hrt_scene* s, void* d_film, const void* peer_handles, int n_peers, int width, int height, int spp,
                              int write_back, void* d_sum_or_null, void* d_mean_or_null, void* d_rgb8_or_null, void* stream);
+
+/* Introspection of a committed scene (tests, tooling): copies one device array of mesh `mesh_index` (world-list order of
+ * first use) into `out` (may be NULL) and returns its size in bytes.  which: 0 reference-topology nodes (32 B each),
+ * 1 fast-tree nodes (64 B), 2 leaf records (128 B), 3 triangle positions (48 B), 4 triangle attributes (64 B). */
+int64_t hrt_scene_mesh_array(hrt_scene* s, int mesh_index, int which, void* out, int64_t capacity_bytes);
 
 int hrt_get_stats(hrt_scene* s, hrt_stats* out);
 int hrt_reset_stats(hrt_scene* s);

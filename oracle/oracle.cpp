@@ -635,6 +635,7 @@ void tonemap_write(V3 c, uint8_t* px)
 // ------------------------------------------------------------------------------------------------------------
 struct BvhBuilder {
     Shape& sh; Rng& rng; std::vector<int> order;
+    bool stable = false;      // bvh_mode >= 2 (HRT_BVH_LBVH_*): equal keys keep their order - the algorithm-independent rule of the GPU builder
     void tri_box(int64_t i, V3& mn, V3& mx) { mn = sh.tri_mn[i]; mx = sh.tri_mx[i]; }
     void child_box(int c, V3& mn, V3& mx) { if (c >= 0) { mn = sh.nodes[c].mn; mx = sh.nodes[c].mx; } else tri_box(~c, mn, mx); }
     int build(size_t start, size_t end)
@@ -649,7 +650,8 @@ struct BvhBuilder {
             if (key(order[start]) < key(order[start + 1])) { left = ~order[start]; right = ~order[start + 1]; }
             else { left = ~order[start + 1]; right = ~order[start]; }
         } else {
-            std::sort(order.begin() + start, order.begin() + end, [&](int a, int b) { return key(a) < key(b); });
+            if (stable) std::stable_sort(order.begin() + start, order.begin() + end, [&](int a, int b) { return key(a) < key(b); });
+            else std::sort(order.begin() + start, order.begin() + end, [&](int a, int b) { return key(a) < key(b); });
             size_t mid = start + n / 2;
             left = build(start, mid);
             right = build(mid, end);
@@ -663,7 +665,7 @@ struct BvhBuilder {
     }
 };
 
-void build_mesh_bvh(Shape& sh, uint64_t seed, int shape_id)
+void build_mesh_bvh(Shape& sh, uint64_t seed, int shape_id, bool stable)
 {
     sh.nodes.clear(); sh.root = -1;
     sh.tri_mn.resize(sh.n_tri); sh.tri_mx.resize(sh.n_tri);
@@ -676,7 +678,7 @@ void build_mesh_bvh(Shape& sh, uint64_t seed, int shape_id)
     }
     if (sh.n_tri == 0) return;
     Rng rng; rng.seed(seed, (uint64_t)shape_id);
-    BvhBuilder b{sh, rng, {}};
+    BvhBuilder b{sh, rng, {}, stable};
     b.order.resize(sh.n_tri); for (int64_t i = 0; i < sh.n_tri; ++i) b.order[i] = (int)i;
     sh.nodes.reserve(sh.n_tri * 2);
     sh.root = b.build(0, (size_t)sh.n_tri);
@@ -757,13 +759,13 @@ int orc_scene_add_medium(orc_scene* s, int shape, const hrt_xform* ops, int n_op
 }
 int orc_scene_set_background(orc_scene* s, int tex) { s->background = tex; return 0; }
 
-int orc_scene_commit(orc_scene* s, int /*bvh_mode*/, uint64_t seed)
+int orc_scene_commit(orc_scene* s, int bvh_mode, uint64_t seed)
 {
     // meshes are built in world-list order, like the reference constructs them while loading (scene.cpp:292-297)
     std::vector<char> done(s->shapes.size(), 0);
     for (Object& o : s->objects) {
         Shape& sh = s->shapes[o.shape];
-        if (sh.kind == 3 && !done[o.shape]) { build_mesh_bvh(sh, seed, o.shape); done[o.shape] = 1; }
+        if (sh.kind == 3 && !done[o.shape]) { build_mesh_bvh(sh, seed, o.shape, bvh_mode >= 2); done[o.shape] = 1; }
     }
     s->committed = true;
     return 0;

@@ -63,6 +63,7 @@ int hsim_scene_set_background(hsim_scene* s, int tex) { B(b_set_background(s->ho
 
 int hsim_scene_commit(hsim_scene* s, int bvh_mode, uint64_t seed)
 {
+    if (bvh_mode == HRT_BVH_LBVH_GPU) bvh_mode = HRT_BVH_LBVH_HOST;     // no device here: the host mirror of the GPU builder
     std::string e = flatten(s->host, bvh_mode, seed);
     if (!e.empty()) { g_err = e; return HRT_ERR_ARG; }
     s->d = make_dscene(s->host, s->up);
@@ -201,5 +202,15 @@ int64_t hsim_mesh_bvh_nodes(hsim_scene* s, int shape, float* boxes, int32_t* chi
             std::memcpy(&children[i * 2], &a.w, 4); std::memcpy(&children[i * 2 + 1], &b.w, 4);
         }
     return (int64_t)n;
+}
+// the arrays hrt_scene_mesh_array returns, from the host builder (HRT_BVH_LBVH_HOST is the mirror of the device builder)
+int64_t hsim_scene_mesh_array(hsim_scene* s, int mesh_index, int which, void* out, int64_t capacity)
+{
+    if (mesh_index < 0 || (size_t)mesh_index >= s->host.mesh_shapes.size() || which < 0 || which > 4) { g_err = "bad argument"; return HRT_ERR_ARG; }
+    const HostShape& sh = s->host.shapes[(size_t)s->host.mesh_shapes[(size_t)mesh_index]];
+    const std::vector<float4>* src[5] = {&sh.ref.nodes, &sh.fast.nodes, &sh.leaves, &sh.tris4, &sh.attrs4};
+    const int64_t bytes = (int64_t)(src[which]->size() * sizeof(float4));
+    if (out) { if (capacity < bytes) { g_err = "buffer too small"; return HRT_ERR_ARG; } if (bytes) std::memcpy(out, src[which]->data(), (size_t)bytes); }
+    return bytes;
 }
 } // extern "C"

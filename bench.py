@@ -61,7 +61,7 @@ def make_workload(name, args):
     elif name == "cornell_smoke":
         sd, cam, info = scenes.cornell_smoke_scene()
     elif name == "big_mesh":
-        sd, cam, info = scenes.big_mesh_scene(CACHE, quads=args.quads)
+        sd, cam, info = scenes.big_mesh_scene(CACHE, quads=args.quads, indexed=args.indexed)
     else:
         raise SystemExit(f"unknown workload {name}")
     w = args.width or info["width"]; h = args.height or info["height"]; spp = args.spp or info["spp"]
@@ -76,6 +76,8 @@ def alg_bytes_per_ray(sd):
     for s in sd.shapes:
         if s[0] == "mesh":
             n_prims += s[1].shape[0]; prim_bytes = 48
+        elif s[0] == "mesh_indexed":
+            n_prims += s[4].shape[0] // 3; prim_bytes = 48
         elif s[0] == "box":
             n_prims += 6; prim_bytes = max(prim_bytes, 32)
         else:
@@ -267,7 +269,7 @@ def run_own(args):
     e2e_step(); sync_all()
     t0 = time.perf_counter(); e2e_rays = 0.0; scene_bytes = 0
     for _ in range(e2e_steps):
-        stt = e2e_step(); e2e_rays += float(stt.rays); scene_bytes = int(stt.scene_bytes)
+        stt = e2e_step(); e2e_rays += float(stt.rays); scene_bytes = int(stt.h2d_bytes)
     sync_all()
     e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
     e2e_r = torch.tensor([e2e_rays], dtype=torch.float64, device="cuda")
@@ -393,6 +395,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="samples per pixel per step (default: the workload's own)")
     ap.add_argument("--width", type=int, default=0); ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--quads", type=int, default=2290)
+    ap.add_argument("--indexed", action="store_true", help="big_mesh: hand the mesh over as vertex / index buffers (hrt_scene_add_mesh_indexed)")
     ap.add_argument("--rays", type=int, default=16 << 20, help="--workload raybatch: total rays")
     ap.add_argument("--bvh", default="sah", choices=["sah", "reference", "lbvh_gpu", "lbvh_host"],
                     help="sah: host binned-SAH trees; lbvh_gpu: the whole per-mesh build on the device (Morton LBVH); lbvh_host: its host mirror")

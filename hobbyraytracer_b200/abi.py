@@ -22,6 +22,7 @@ XF_TRANSLATE, XF_SCALE, XF_ROTATE_QUAT, XF_ROTATE_Y, XF_ROTATE_EULER_DEG, XF_ROT
 BVH_REFERENCE, BVH_SAH, BVH_LBVH_GPU, BVH_LBVH_HOST = range(4)
 RENDER_MEGAKERNEL = 1
 RENDER_WAVEFRONT_V1 = 2
+MESH_BORROW = 1
 
 
 class Material(C.Structure):
@@ -48,7 +49,8 @@ class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("paths", C.c_uint64), ("launches", C.c_uint64), ("ms_trace", C.c_double),
                 ("ms_shade", C.c_double), ("ms_other", C.c_double), ("ms_total", C.c_double),
                 ("node_tests", C.c_uint64), ("prim_tests", C.c_uint64), ("retraced", C.c_uint64),
-                ("scene_bytes", C.c_uint64), ("ms_build", C.c_double)]
+                ("scene_bytes", C.c_uint64), ("ms_build", C.c_double),
+                ("h2d_bytes", C.c_uint64), ("ms_build_upload", C.c_double)]
 
 
 def make_camera(position, look_at, up, vfov_deg, aspect, aperture=0.0, focal_distance=1.0) -> Camera:
@@ -109,6 +111,7 @@ class Lib:
         self._sig("scene_add_rect", i, [_vp, i, f32, f32, f32, f32, f32, i])
         self._sig("scene_add_box", i, [_vp, _vp, _vp, i])
         self._sig("scene_add_mesh", i, [_vp, _vp, _vp, _vp, i64, i])
+        self._sig("scene_add_mesh_indexed", i, [_vp, _vp, _vp, _vp, i64, _vp, i64, _vp, i, i, C.c_uint32], required=False)
         self._sig("scene_prim_base", i64, [_vp, i])
         self._sig("scene_prim_count", i64, [_vp])
         self._sig("scene_add_object", i, [_vp, i, _vp, i])
@@ -165,6 +168,8 @@ class SceneDesc:
     """A scene as a list of reference constructor calls; replay with `.build(lib)`."""
     textures: list = field(default_factory=list)      # ("solid", rgb) | ("checker", even, odd) | ("image", u8[h,w,3]) | ("env", f32[h,w,c]) | ("env_file", path, f32[h,w,c])
     materials: list = field(default_factory=list)     # dict(kind=, albedo=, albedo_tex=, p0=, p0_tex=, p1=, p1_tex=)
+    borrow: bool = False                              # mesh_indexed shapes: pass HRT_MESH_BORROW (the arrays live in self.shapes until build() returns)
+    flatten_for_all: bool = False                     # mesh_indexed shapes: flatten in numpy even for libraries that have the indexed entry
     shapes: list = field(default_factory=list)        # ("sphere", c, r, mat) | ("rect", axis, a0,a1,b0,b1,k, mat) | ("box", center, dims, mat) | ("mesh", pos, nrm, uv, mat)
     objects: list = field(default_factory=list)       # ("object", shape, ops) | ("medium", shape, ops, density, rgb, tex)
     background: Optional[int] = None
@@ -206,6 +211,33 @@ class SceneDesc:
         nrm = None if nrm is None else _f32(nrm).reshape(-1, 9)
         uv = None if uv is None else _f32(uv).reshape(-1, 6)
         self.shapes.append(("mesh", pos, nrm, uv, mat)); return len(self.shapes) - 1
+
+    def mesh_indexed(self, vertices, normals, uvs, indices, mat, submeshes=None) -> int:
+        """hrt_scene_add_mesh_indexed: per-vertex arrays + an index buffer as Mesh::assimpLoadFile concatenates them
+        (mesh.cpp:63-115); submeshes = [(first_index, n_index, base_vertex), ...] applies the base-vertex offset the reference
+        leaves out (mesh.cpp:111-114).  Libraries without the entry point (oracle, reference harness) get the triangles
+        flattened here exactly like Mesh::Mesh's loop (mesh.cpp:24-33)."""
+        v = _f32(vertices).reshape(-1, 3)
+        n = None if normals is None else _f32(normals).reshape(-1, 3)
+        t = None if uvs is None else _f32(uvs).reshape(-1, 2)
+        idx = np.ascontiguousarray(indices, dtype=np.uint32).reshape(-1)
+        sub = None if submeshes is None else np.ascontiguousarray(submeshes, dtype=np.int64).reshape(-1, 3)
+        self.shapes.append(("mesh_indexed", v, n, t, idx, sub, mat)); return len(self.shapes) - 1
+
+    @staticmethod
+    def flatten_indexed(v, n, t, idx, sub):
+        """numpy restatement of Mesh::Mesh's gather (mesh.cpp:24-33) -> (pos [T,9], nrm [T,9], uv [T,6])"""
+        idx = idx.astype(np.int64)
+        if sub is not None:
+            idx = idx.copy()
+            for first, count, base in sub:
+                idx[first:first + count] += base
+        if n is None:
+            n = np.zeros_like(v)
+        if t is None:
+            t = np.zeros((v.shape[0], 2), np.float32)
+        return (np.ascontiguousarray(v[idx].reshape(-1, 9)), np.ascontiguousarray(n[idx].reshape(-1, 9)),
+                np.ascontiguousarray(t[idx].reshape(-1, 6)))
 
     def add(self, shape: int, ops: Sequence[Tuple] = ()) -> None:
         self.objects.append(("object", shape, list(ops)))
@@ -252,6 +284,15 @@ class SceneDesc:
             elif s[0] == "mesh":
                 _, pos, nrm, uv, mat = s
                 lib.check(lib.fn("scene_add_mesh")(h, _ptr(pos), _ptr(nrm), _ptr(uv), pos.shape[0], mat), "add_mesh")
+            elif s[0] == "mesh_indexed":
+                _, v, n, t, idx, sub, mat = s
+                if lib.has("scene_add_mesh_indexed") and not self.flatten_for_all:
+                    lib.check(lib.fn("scene_add_mesh_indexed")(h, _ptr(v), _ptr(n), _ptr(t), v.shape[0], _ptr(idx), idx.shape[0],
+                                                                _ptr(sub), 0 if sub is None else sub.shape[0], mat,
+                                                                MESH_BORROW if self.borrow else 0), "add_mesh_indexed")   # self.shapes keeps the arrays alive
+                else:
+                    pos, nrm, uv = self.flatten_indexed(v, n, t, idx, sub)
+                    lib.check(lib.fn("scene_add_mesh")(h, _ptr(pos), _ptr(nrm), _ptr(uv), pos.shape[0], mat), "add_mesh")
         for o in self.objects:
             ops = o[2]
             arr = (Xform * max(1, len(ops)))()

@@ -55,7 +55,7 @@ struct hrt_scene {
     int device = 0, sm_count = 148;
     cudaStream_t stream = nullptr;
     std::vector<void*> scene_allocs;
-    size_t scene_bytes = 0;
+    size_t scene_bytes = 0, h2d_bytes = 0; double ms_build_upload = 0;
     // persistent-wavefront working set
     WaveJob job{};
     unsigned int job_capacity = 0;
@@ -288,6 +288,8 @@ int hrt_scene_add_sphere(hrt_scene* s, const float c[3], float r, int m) { NEED(
 int hrt_scene_add_rect(hrt_scene* s, int axis, float a0, float a1, float b0, float b1, float k, int m) { NEED(s); return b_add_rect(s->host, axis, a0, a1, b0, b1, k, m, g_err); }
 int hrt_scene_add_box(hrt_scene* s, const float c[3], const float d[3], int m) { NEED(s); return b_add_box(s->host, c, d, m, g_err); }
 int hrt_scene_add_mesh(hrt_scene* s, const float* p, const float* n, const float* uv, int64_t nt, int m) { NEED(s); return b_add_mesh(s->host, p, n, uv, nt, m, g_err); }
+int hrt_scene_add_mesh_indexed(hrt_scene* s, const float* v, const float* n, const float* uv, int64_t nv, const uint32_t* idx, int64_t ni,
+                               const hrt_submesh* sub, int n_sub, int m, uint32_t flags) { NEED(s); return b_add_mesh_indexed(s->host, v, n, uv, nv, idx, ni, sub, n_sub, m, flags, g_err); }
 int hrt_scene_add_object(hrt_scene* s, int shape, const hrt_xform* ops, int n) { NEED(s); return b_add_object(s->host, shape, ops, n, g_err); }
 int hrt_scene_add_medium(hrt_scene* s, int shape, const hrt_xform* ops, int n, float density, const float rgb[3], int tex) { NEED(s); return b_add_medium(s->host, shape, ops, n, density, rgb, tex, g_err); }
 int hrt_scene_set_background(hrt_scene* s, int tex) { NEED(s); return b_set_background(s->host, tex, g_err); }
@@ -308,13 +310,16 @@ int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed)
     std::string e = flatten(s->host, bvh_mode, seed);
     if (!e.empty()) { g_err = e; return HRT_ERR_ARG; }
     CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-    s->ms_build_gpu = 0; s->bvh_fallbacks = 0;
+    s->ms_build_gpu = 0; s->bvh_fallbacks = 0; s->h2d_bytes = 0; s->ms_build_upload = 0;
     size_t dev_bytes = 0;
     for (int shape : s->host.mesh_shapes) {                       // HRT_BVH_LBVH_GPU: per-mesh arrays are built on the device
         HostShape& sh = s->host.shapes[(size_t)shape];
         if (!sh.gpu_pending) continue;
         GpuMeshBuild b; std::string berr;
-        if (!build_mesh_gpu(sh.pos.data(), sh.nrm.data(), sh.uv.data(), sh.n_tri, seed, shape, s->stream, s->scene_allocs, dev_bytes, b, berr, &s->stats.launches)) {
+        MeshSource src;
+        if (sh.indexed) { src.indexed = true; src.pos = sh.V(); src.nrm = sh.N(); src.uv = sh.T(); src.idx = sh.I(); src.n_vert = sh.n_vert; }
+        else { src.pos = sh.pos.data(); src.nrm = sh.nrm.data(); src.uv = sh.uv.data(); }
+        if (!build_mesh_gpu(src, sh.n_tri, seed, shape, s->stream, s->scene_allocs, dev_bytes, b, berr, &s->stats.launches)) {
             g_err = "device BVH build failed: " + berr; free_scene_device(s); return HRT_ERR_CUDA;
         }
         sh.gpu_pending = false;
@@ -327,16 +332,19 @@ int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed)
         sh.has_dev = true; sh.dev = b.mesh;
         sh.n_ref_nodes = b.n_ref_nodes; sh.n_fast_nodes = b.n_fast_nodes; sh.n_leaves = b.n_leaves; sh.last_tri_r = b.last_tri_r;
         sh.fast.depth = b.depth;
-        s->ms_build_gpu += b.ms_upload + b.ms_build;
+        s->ms_build_gpu += b.ms_upload + b.ms_build; s->ms_build_upload += b.ms_upload; s->h2d_bytes += b.h2d_bytes;
+        if (getenv("HRT_DEBUG_BUILD")) fprintf(stderr, "[hrt] device build of shape %d: %lld triangles, source %.1f MB (%s) uploaded in %.1f ms, built in %.1f ms\n",
+                                               shape, (long long)sh.n_tri, b.h2d_bytes / 1e6, sh.indexed ? "indexed" : "soup", b.ms_upload, b.ms_build);
     }
     DevUp up(s->scene_allocs);
     s->d = make_dscene(s->host, up);
     if (const char* e = getenv("HRT_REFILL_SECONDARY")) s->d.refill_secondary = (atoi(e) != 0 && s->d.fast) ? 1 : 0;   // A/B override
     if (up.failed) { g_err = "scene upload failed: " + up.msg; free_scene_device(s); return HRT_ERR_CUDA; }
-    s->scene_bytes = up.bytes + dev_bytes;
+    s->scene_bytes = up.bytes + dev_bytes; s->h2d_bytes += up.bytes;
     s->meshes_view.resize(s->host.mesh_shapes.size());
     if (!s->meshes_view.empty()) CK(cudaMemcpy(s->meshes_view.data(), s->d.meshes, s->meshes_view.size() * sizeof(DMesh), cudaMemcpyDeviceToHost));
     CK(cudaDeviceSynchronize());
+    for (HostShape& sh : s->host.shapes) sh.release_borrowed();   // HRT_MESH_BORROW ends here
     s->host.committed = true;
     return 0;
 }
@@ -506,7 +514,7 @@ int hrt_film_resolve_peers(hrt_scene* s, void* d_film, const void* peer_handles,
 int hrt_get_stats(hrt_scene* s, hrt_stats* out)
 {
     if (!s || !out) { g_err = "NULL argument"; return HRT_ERR_ARG; }
-    *out = s->stats; out->scene_bytes = s->scene_bytes; out->ms_build = s->host.build_ms_ref + s->host.build_ms_fast + s->ms_build_gpu;
+    *out = s->stats; out->scene_bytes = s->scene_bytes; out->h2d_bytes = s->h2d_bytes; out->ms_build_upload = s->ms_build_upload; out->ms_build = s->host.build_ms_ref + s->host.build_ms_fast + s->ms_build_gpu;
     return 0;
 }
 int hrt_reset_stats(hrt_scene* s)

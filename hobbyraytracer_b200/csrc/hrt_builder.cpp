@@ -2,6 +2,7 @@
 // construction site of the reference's loader (scene.cpp:184-211 textures, 246-264 materials, 292-353 objects).
 // Argument checking lives here so that the CUDA entry points and the CPU simulation harness share it.
 #include <cstring>
+#include <thread>
 
 #include "hrt_host.h"
 
@@ -87,6 +88,96 @@ int b_add_mesh(HostScene& s, const float* pos, const float* nrm, const float* uv
     if (nrm) d.nrm.assign(nrm, nrm + n_tri * 9); else d.nrm.assign((size_t)n_tri * 9, 0.0f);   // mesh.cpp:87-99
     if (uv) d.uv.assign(uv, uv + n_tri * 6); else d.uv.assign((size_t)n_tri * 6, 0.0f);
     return push_shape(s, std::move(d), n_tri);
+}
+
+// n items in at most hardware_concurrency() contiguous chunks of at least min_chunk, one thread each; chunk c covers
+// [begin, end) and chunks are numbered in array order (so per-chunk results can be combined in a fixed order)
+static size_t chunk_count(size_t n, size_t min_chunk)
+{
+    size_t nt = std::thread::hardware_concurrency(); if (nt < 1) nt = 1; if (nt > 32) nt = 32;
+    size_t k = min_chunk ? n / min_chunk : nt; if (k < 1) k = 1; if (k > nt) k = nt;
+    return k;
+}
+void parallel_chunks(size_t n, size_t min_chunk, const std::function<void(size_t, size_t, size_t)>& fn, size_t* n_chunks)
+{
+    const size_t k = chunk_count(n, min_chunk);
+    if (n_chunks) *n_chunks = k;
+    if (k == 1) { fn(0, 0, n); return; }
+    std::vector<std::thread> th;
+    for (size_t c = 0; c < k; ++c) th.emplace_back([&, c]() { fn(c, n * c / k, n * (c + 1) / k); });
+    for (std::thread& t : th) t.join();
+}
+
+int b_add_mesh_indexed(HostScene& s, const float* vtx, const float* nrm, const float* uv, int64_t n_vert, const uint32_t* idx, int64_t n_idx,
+                       const hrt_submesh* sub, int n_sub, int material, uint32_t flags, std::string& err)
+{
+    if (n_vert < 0 || n_idx < 0 || (n_vert > 0 && !vtx) || (n_idx > 0 && !idx)) return fail(err, "bad mesh arguments");
+    if (flags & ~HRT_MESH_BORROW) return fail(err, "unknown mesh flags");
+    if (n_idx % 3 != 0) return fail(err, "index count is not a multiple of 3");
+    if (n_vert > 0xffffffffll) return fail(err, "more vertices than 32-bit indices can address");
+    const int64_t n_tri = n_idx / 3;
+    if (n_tri > 0x7fffffff / 3) return fail(err, "mesh too large for 32-bit node ids");
+    if (n_sub < 0 || (n_sub > 0 && !sub)) return fail(err, "bad sub-mesh table");
+    if (!mat_ok(s, material)) return fail(err, "unknown material");
+    const bool borrow = (flags & HRT_MESH_BORROW) != 0;
+    HostShape d; d.kind = SHAPE_MESH; d.n_tri = n_tri; d.material = material; d.indexed = true; d.n_vert = n_vert;
+    if (sub) {                                                                  // the offset mesh.cpp:111-114 leaves out
+        d.vidx.assign(idx, idx + n_idx);
+        std::vector<uint8_t> seen((size_t)n_idx, 0);
+        for (int m = 0; m < n_sub; ++m) {
+            const hrt_submesh& q = sub[m];
+            if (q.first_index < 0 || q.n_index < 0 || q.first_index > n_idx || q.n_index > n_idx - q.first_index || q.n_index % 3 != 0 || q.first_index % 3 != 0)
+                return fail(err, "sub-mesh index range out of bounds");
+            if (q.base_vertex < 0 || q.base_vertex > n_vert) return fail(err, "sub-mesh base vertex out of bounds");
+            for (int64_t j = q.first_index; j < q.first_index + q.n_index; ++j) {
+                if (seen[(size_t)j]) return fail(err, "sub-mesh index ranges overlap");
+                seen[(size_t)j] = 1;
+                const uint64_t v = (uint64_t)idx[j] + (uint64_t)q.base_vertex;
+                if (v >= (uint64_t)n_vert) return fail(err, "vertex index out of range");
+                d.vidx[(size_t)j] = (uint32_t)v;
+            }
+        }
+        for (int64_t j = 0; j < n_idx; ++j) if (!seen[(size_t)j]) return fail(err, "sub-mesh table does not cover every index");
+    } else {
+        std::vector<uint8_t> bad(64, 0);
+        if (!borrow) d.vidx.resize((size_t)n_idx);
+        uint32_t* copy = borrow ? nullptr : d.vidx.data();
+        parallel_chunks((size_t)n_idx, 1 << 20, [&](size_t c, size_t b, size_t e) {      // range check (+ the copy) in one pass
+            uint32_t worst = 0;
+            if (copy) for (size_t j = b; j < e; ++j) { const uint32_t q = idx[j]; copy[j] = q; worst = q > worst ? q : worst; }
+            else for (size_t j = b; j < e; ++j) { const uint32_t q = idx[j]; worst = q > worst ? q : worst; }
+            if ((int64_t)worst >= n_vert && e > b) bad[c] = 1;
+        });
+        for (uint8_t b : bad) if (b) return fail(err, "vertex index out of range");
+    }
+    if (d.vidx.empty()) d.pi = idx;                                             // borrowed (or no indices at all)
+    auto take = [&](std::vector<float>& own, const float*& view, const float* src, size_t count) {
+        if (src && borrow) { view = src; return; }
+        if (src) {
+            own.resize(count);
+            float* dst = own.data();
+            parallel_chunks(count, 1 << 22, [&](size_t, size_t b, size_t e) { std::memcpy(dst + b, src + b, (e - b) * sizeof(float)); });
+        } else own.assign(count, 0.0f);                                         // mesh.cpp:87-99: zeros when the file has none
+    };
+    take(d.vpos, d.pv, vtx, (size_t)n_vert * 3);
+    take(d.vnrm, d.pn, nrm, (size_t)n_vert * 3);
+    take(d.vuv, d.pt, uv, (size_t)n_vert * 2);
+    return push_shape(s, std::move(d), n_tri);
+}
+
+void ensure_soup(HostShape& sh)
+{
+    if (!sh.indexed || sh.pos.size() == (size_t)sh.n_tri * 9) return;
+    const size_t n = (size_t)sh.n_tri;
+    sh.pos.resize(n * 9); sh.nrm.resize(n * 9); sh.uv.resize(n * 6);
+    const float *V = sh.V(), *N = sh.N(), *T = sh.T(); const uint32_t* I = sh.I();
+    parallel_chunks(n * 3, 1 << 18, [&](size_t, size_t b, size_t e) {
+        for (size_t c = b; c < e; ++c) {                                        // corner c = triangle c/3, vertex c%3 (mesh.cpp:26-29)
+            const size_t v = I[c];
+            for (int a = 0; a < 3; ++a) { sh.pos[c * 3 + a] = V[v * 3 + a]; sh.nrm[c * 3 + a] = N[v * 3 + a]; }
+            sh.uv[c * 2] = T[v * 2]; sh.uv[c * 2 + 1] = T[v * 2 + 1];
+        }
+    });
 }
 
 static int fill_ops(HostObject& o, const hrt_xform* ops, int n_ops, std::string& err)

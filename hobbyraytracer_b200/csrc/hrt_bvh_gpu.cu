@@ -34,17 +34,31 @@ __device__ __forceinline__ int as_i(float f) { return __float_as_int(f); }
 __device__ __forceinline__ float as_f(int i) { return __int_as_float(i); }
 
 // flags[0] != 0: some position is not finite (keys would not be ordered; the host path takes over)
-__global__ void k_mesh_pack(const float* __restrict__ pos, const float* __restrict__ nrm, const float* __restrict__ uv, long long n,
+// INDEXED: pos / nrm / uv are per-vertex arrays (3 + 3 + 2 floats) and corner v of triangle i is vertex idx[3i + v] -
+// Mesh::Mesh's gather (mesh.cpp:24-33) fused into the packing pass
+template <bool INDEXED>
+__global__ void k_mesh_pack(const float* __restrict__ pos, const float* __restrict__ nrm, const float* __restrict__ uv,
+                            const unsigned int* __restrict__ idx, long long n,
                             float4* __restrict__ tris, float4* __restrict__ attrs, float4* __restrict__ tmin, float4* __restrict__ tmax,
                             unsigned int* __restrict__ order, int* __restrict__ flags)
 {
     long long i = (long long)blockIdx.x * TB + threadIdx.x;
     if (i >= n) return;
     float P[9], N[9], T[6];
-    #pragma unroll
-    for (int k = 0; k < 9; ++k) { P[k] = __ldg(pos + i * 9 + k); N[k] = __ldg(nrm + i * 9 + k); }
-    #pragma unroll
-    for (int k = 0; k < 6; ++k) T[k] = __ldg(uv + i * 6 + k);
+    if (INDEXED) {
+        #pragma unroll
+        for (int v = 0; v < 3; ++v) {
+            const size_t q = __ldg(idx + i * 3 + v);
+            #pragma unroll
+            for (int a = 0; a < 3; ++a) { P[v * 3 + a] = __ldg(pos + q * 3 + a); N[v * 3 + a] = __ldg(nrm + q * 3 + a); }
+            T[v * 2] = __ldg(uv + q * 2); T[v * 2 + 1] = __ldg(uv + q * 2 + 1);
+        }
+    } else {
+        #pragma unroll
+        for (int k = 0; k < 9; ++k) { P[k] = __ldg(pos + i * 9 + k); N[k] = __ldg(nrm + i * 9 + k); }
+        #pragma unroll
+        for (int k = 0; k < 6; ++k) T[k] = __ldg(uv + i * 6 + k);
+    }
     bool bad = false;
     #pragma unroll
     for (int k = 0; k < 9; ++k) bad |= !(fabsf(P[k]) <= 3.0e38f);
@@ -251,7 +265,7 @@ inline int bits_for(uint64_t v) { int b = 0; while (v) { ++b; v >>= 1; } return 
 
 #define GB_CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = std::string(#x) + ": " + cudaGetErrorString(e_); return false; } } while (0)
 
-bool build_mesh_gpu(const float* pos, const float* nrm, const float* uv, int64_t n_tri, uint64_t seed, int shape_id,
+bool build_mesh_gpu(const MeshSource& src, int64_t n_tri, uint64_t seed, int shape_id,
                     cudaStream_t st, std::vector<void*>& allocs, size_t& bytes, GpuMeshBuild& out, std::string& err, uint64_t* launches)
 {
     out = GpuMeshBuild();
@@ -266,8 +280,10 @@ bool build_mesh_gpu(const float* pos, const float* nrm, const float* uv, int64_t
     const size_t allocs_at_entry = allocs.size(); const size_t bytes_at_entry = bytes;
     auto drop_results = [&]() { while (allocs.size() > allocs_at_entry) { cudaFree(allocs.back()); allocs.pop_back(); } bytes = bytes_at_entry; };
     float *d_pos, *d_nrm, *d_uv; float4 *d_tmin, *d_tmax; unsigned int *d_order[2]; unsigned long long* d_keys[2];
-    uint8_t* d_axis; int* d_flags;
-    if (!tmp.get(d_pos, n * 9) || !tmp.get(d_nrm, n * 9) || !tmp.get(d_uv, n * 6) || !tmp.get(d_tmin, n) || !tmp.get(d_tmax, n) ||
+    uint8_t* d_axis; int* d_flags; unsigned int* d_idx = nullptr;
+    const size_t n_in = src.indexed ? (size_t)src.n_vert : n * 3;        // vertices that cross PCIe
+    if (src.indexed && !tmp.get(d_idx, n * 3)) { err = "out of device memory (index buffer)"; return false; }
+    if (!tmp.get(d_pos, n_in * 3) || !tmp.get(d_nrm, n_in * 3) || !tmp.get(d_uv, n_in * 2) || !tmp.get(d_tmin, n) || !tmp.get(d_tmax, n) ||
         !tmp.get(d_order[0], n) || !tmp.get(d_order[1], n) || !tmp.get(d_keys[0], n) || !tmp.get(d_keys[1], n) ||
         !tmp.get(d_axis, n_nodes) || !tmp.get(d_flags, 16)) { err = "out of device memory (BVH build scratch)"; return false; }
     // results (owned by the scene)
@@ -275,16 +291,20 @@ bool build_mesh_gpu(const float* pos, const float* nrm, const float* uv, int64_t
     auto keep = [&](float4*& p, size_t count) { void* v = nullptr; if (cudaMalloc(&v, (count ? count : 1) * sizeof(float4)) != cudaSuccess) return false; allocs.push_back(v); bytes += count * sizeof(float4); p = (float4*)v; return true; };
     if (!keep(d_tris, n * 3) || !keep(d_attrs, n * 4) || !keep(d_ref, n_nodes * 2) || !keep(d_leaves, n_leaves * 8) || !keep(d_fast, n_leaves > 1 ? (n_leaves - 1) * 4 : 0)) { err = "out of device memory (mesh arrays)"; return false; }
 
-    GB_CK(cudaMemcpyAsync(d_pos, pos, n * 9 * sizeof(float), cudaMemcpyHostToDevice, st));
-    GB_CK(cudaMemcpyAsync(d_nrm, nrm, n * 9 * sizeof(float), cudaMemcpyHostToDevice, st));
-    GB_CK(cudaMemcpyAsync(d_uv, uv, n * 6 * sizeof(float), cudaMemcpyHostToDevice, st));
+    GB_CK(cudaMemcpyAsync(d_pos, src.pos, n_in * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+    GB_CK(cudaMemcpyAsync(d_nrm, src.nrm, n_in * 3 * sizeof(float), cudaMemcpyHostToDevice, st));
+    GB_CK(cudaMemcpyAsync(d_uv, src.uv, n_in * 2 * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (src.indexed) GB_CK(cudaMemcpyAsync(d_idx, src.idx, n * 3 * sizeof(unsigned int), cudaMemcpyHostToDevice, st));
+    out.h2d_bytes = n_in * 8 * sizeof(float) + (src.indexed ? n * 3 * sizeof(unsigned int) : 0);
     GB_CK(cudaMemsetAsync(d_flags, 0, 16 * sizeof(int), st));
     GB_CK(cudaStreamSynchronize(st));
     out.ms_upload = now_ms() - t_begin;
     const double t_build = now_ms();
     uint64_t nl = 0;
 
-    k_mesh_pack<<<grid_for((long long)n), TB, 0, st>>>(d_pos, d_nrm, d_uv, (long long)n, d_tris, d_attrs, d_tmin, d_tmax, d_order[0], d_flags); ++nl;
+    if (src.indexed) k_mesh_pack<true><<<grid_for((long long)n), TB, 0, st>>>(d_pos, d_nrm, d_uv, d_idx, (long long)n, d_tris, d_attrs, d_tmin, d_tmax, d_order[0], d_flags);
+    else k_mesh_pack<false><<<grid_for((long long)n), TB, 0, st>>>(d_pos, d_nrm, d_uv, nullptr, (long long)n, d_tris, d_attrs, d_tmin, d_tmax, d_order[0], d_flags);
+    ++nl;
     const uint64_t stream0 = rule_mix64(seed ^ rule_mix64((uint64_t)shape_id));
     k_node_axes<<<grid_for((long long)n_nodes), TB, 0, st>>>(stream0, (long long)n_nodes, d_axis); ++nl;
 

@@ -18,12 +18,22 @@ struct GpuMeshBuild {
     bool fallback = false;           // true: this mesh cannot be built here (why), the host builder takes over
     std::string why;
     double ms_upload = 0, ms_build = 0;
+    size_t h2d_bytes = 0;            // bytes of mesh source copied host -> device
 };
 
-// Uploads the raw triangle soup (9 + 9 + 6 floats per triangle, the layout of hrt_scene_add_mesh) and builds every
-// per-mesh array on the device.  Result allocations are appended to `allocs` (owned by the scene).  Returns false with
-// `err` set on a CUDA failure.
-bool build_mesh_gpu(const float* pos, const float* nrm, const float* uv, int64_t n_tri, uint64_t seed, int shape_id,
+// Host-side view of one mesh: the raw triangle soup (9 + 9 + 6 floats per triangle, the layout of hrt_scene_add_mesh), or
+// - indexed - per-vertex arrays (3 + 3 + 2 floats) with 3 indices per triangle (hrt_scene_add_mesh_indexed)
+struct MeshSource {
+    const float *pos = nullptr, *nrm = nullptr, *uv = nullptr;
+    const uint32_t* idx = nullptr;
+    int64_t n_vert = 0;
+    bool indexed = false;
+};
+
+// Uploads the mesh source and builds every per-mesh array on the device (an indexed source is gathered there, so only
+// the compact buffers cross PCIe).  Result allocations are appended to `allocs` (owned by the scene).  Returns false
+// with `err` set on a CUDA failure.
+bool build_mesh_gpu(const MeshSource& src, int64_t n_tri, uint64_t seed, int shape_id,
                     cudaStream_t st, std::vector<void*>& allocs, size_t& bytes, GpuMeshBuild& out, std::string& err, uint64_t* launches);
 
 } // namespace hrt

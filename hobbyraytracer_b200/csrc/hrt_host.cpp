@@ -500,8 +500,21 @@ DBox world_bounds(const HostShape& sh, const HostObject& o)
             b.mn[a] = std::min(lo, hi); b.mx[a] = std::max(lo, hi);
         } break;
     case SHAPE_MESH:
-        for (int64_t i = 0; i < sh.n_tri * 3; ++i)
-            for (int a = 0; a < 3; ++a) { double v = sh.pos[(size_t)i * 3 + a]; b.mn[a] = std::min(b.mn[a], v); b.mx[a] = std::max(b.mx[a], v); }
+        {   // every corner, through the index buffer when there is one.  Contiguous chunks, combined in array order: the
+            // same first-of-equals result as one sequential pass
+            const float* V = sh.indexed ? sh.V() : sh.pos.data(); const uint32_t* I = sh.indexed ? sh.I() : nullptr;
+            std::vector<DBox> part(64, b); size_t used = 1;
+            parallel_chunks((size_t)sh.n_tri * 3, 1 << 18, [&](size_t c, size_t lo, size_t hi) {
+                DBox q = part[c];
+                for (size_t i = lo; i < hi; ++i) {
+                    const float* P = V + (I ? (size_t)I[i] : i) * 3;
+                    for (int a = 0; a < 3; ++a) { double v = P[a]; q.mn[a] = std::min(q.mn[a], v); q.mx[a] = std::max(q.mx[a], v); }
+                }
+                part[c] = q;
+            }, &used);
+            for (size_t c = 0; c < used; ++c)
+                for (int a = 0; a < 3; ++a) { b.mn[a] = std::min(b.mn[a], part[c].mn[a]); b.mx[a] = std::max(b.mx[a], part[c].mx[a]); }
+        }
         if (sh.n_tri == 0) for (int a = 0; a < 3; ++a) { b.mn[a] = 0; b.mx[a] = 0; }
         break;
     default: break;
@@ -546,6 +559,7 @@ void build_mesh_host(HostShape& sh, int bvh_mode, uint64_t seed, int shape_id, i
 {
     const bool fast = bvh_mode != HRT_BVH_REFERENCE;
     const bool lbvh = bvh_mode == HRT_BVH_LBVH_HOST || bvh_mode == HRT_BVH_LBVH_GPU;
+    ensure_soup(sh);
     double t0 = now_ms();
     build_ref_bvh(sh, seed, shape_id, nt, lbvh);
     ms_ref += now_ms() - t0;

@@ -2,6 +2,7 @@
 // flattens them into the arrays of hrt_types.h.  No CUDA in here (plain C++17).
 #pragma once
 #include <cstdint>
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -46,7 +47,20 @@ struct HostShape {
     float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     int axis = 0;
     int material = -1;
-    std::vector<float> pos, nrm, uv;
+    std::vector<float> pos, nrm, uv;     // triangle soup: 9 + 9 + 6 floats per triangle (hrt_scene_add_mesh)
+    // hrt_scene_add_mesh_indexed: vertex / index buffers (indices already carry their sub-mesh's base vertex); the soup
+    // above stays empty until a host builder needs it (ensure_soup) - the device builder gathers through the indices
+    bool indexed = false;
+    std::vector<float> vpos, vnrm, vuv;  // 3 + 3 + 2 floats per vertex (owned copies; empty when borrowed)
+    std::vector<uint32_t> vidx;          // 3 per triangle
+    const float *pv = nullptr, *pn = nullptr, *pt = nullptr;   // HRT_MESH_BORROW: the caller's arrays (valid until the commit
+    const uint32_t* pi = nullptr;                              // returns, dropped by release_borrowed), else NULL
+    const float* V() const { return pv ? pv : vpos.data(); }   // what the builders read
+    const float* N() const { return pn ? pn : vnrm.data(); }
+    const float* T() const { return pt ? pt : vuv.data(); }
+    const uint32_t* I() const { return pi ? pi : vidx.data(); }
+    void release_borrowed() { pv = pn = pt = nullptr; pi = nullptr; }
+    int64_t n_vert = 0;
     int64_t n_tri = 0;
     int64_t prim_base = 0, prim_count = 0;
     bool used = false;
@@ -129,6 +143,10 @@ int b_add_sphere(HostScene& s, const float c[3], float radius, int material, std
 int b_add_rect(HostScene& s, int axis, float a0, float a1, float b0, float b1, float k, int material, std::string& err);
 int b_add_box(HostScene& s, const float c[3], const float dim[3], int material, std::string& err);
 int b_add_mesh(HostScene& s, const float* pos, const float* nrm, const float* uv, int64_t n_tri, int material, std::string& err);
+int b_add_mesh_indexed(HostScene& s, const float* vtx, const float* nrm, const float* uv, int64_t n_vert, const uint32_t* idx, int64_t n_idx,
+                       const hrt_submesh* sub, int n_sub, int material, uint32_t flags, std::string& err);
+void parallel_chunks(size_t n, size_t min_chunk, const std::function<void(size_t chunk, size_t begin, size_t end)>& fn, size_t* n_chunks = nullptr);
+void ensure_soup(HostShape& sh);         // indexed mesh: materialise pos / nrm / uv (mesh.cpp:24-33) for the host builders
 int b_add_object(HostScene& s, int shape, const hrt_xform* ops, int n_ops, std::string& err);
 int b_add_medium(HostScene& s, int shape, const hrt_xform* ops, int n_ops, float density, const float rgb[3], int albedo_tex, std::string& err);
 int b_set_background(HostScene& s, int tex, std::string& err);

@@ -21,8 +21,10 @@ F = np.float32
 # ---------------------------------------------------------------------------------------------------------------
 # meshes (per-triangle-corner arrays: pos n x 9, nrm n x 9, uv n x 6 — what mesh.cpp:24-35 feeds ITriangle)
 # ---------------------------------------------------------------------------------------------------------------
-def grid_mesh(nu: int, nv: int, fn, flip: bool = False):
-    """Tessellate a parametric surface p(u,v), n(u,v) on an nu x nv quad grid -> 2*nu*nv triangles."""
+def grid_mesh(nu: int, nv: int, fn, flip: bool = False, indexed: bool = False):
+    """Tessellate a parametric surface p(u,v), n(u,v) on an nu x nv quad grid -> 2*nu*nv triangles.
+    indexed: -> (vertices [V,3], normals [V,3], uvs [V,2], indices [6*nu*nv] u32) whose flattening (mesh.cpp:24-33) is
+    exactly the triangle soup the default form returns."""
     u = np.linspace(0.0, 1.0, nu + 1)
     v = np.linspace(0.0, 1.0, nv + 1)
     uu, vv = np.meshgrid(u, v, indexing="ij")
@@ -38,6 +40,10 @@ def grid_mesh(nu: int, nv: int, fn, flip: bool = False):
         t = np.stack([t0, t1], 2)           # (nu, nv, 2, 3, c)
         return t.reshape(-1, 3 * a.shape[-1])
 
+    if indexed:
+        ids = np.arange((nu + 1) * (nv + 1), dtype=np.int64).reshape(nu + 1, nv + 1, 1)
+        return (P.reshape(-1, 3).astype(F), N.reshape(-1, 3).astype(F), UV.reshape(-1, 2).astype(F),
+                corners(ids).reshape(-1).astype(np.uint32))
     return corners(P).astype(F), corners(N).astype(F), corners(UV).astype(F)
 
 
@@ -59,7 +65,7 @@ def _value_noise(x, y, seed, octaves=4):
     return out
 
 
-def blob_mesh(nu: int, nv: int, radius: float = 1.0, bump: float = 0.15, seed: int = 7, center=(0.0, 0.0, 0.0)):
+def blob_mesh(nu: int, nv: int, radius: float = 1.0, bump: float = 0.15, seed: int = 7, center=(0.0, 0.0, 0.0), indexed: bool = False):
     """A noise-displaced UV sphere ("teapot-scale" / "statue-scale" stand-in). 2*nu*nv triangles.
     Normals are the analytic sphere normals (smooth shading)."""
     def fn(uu, vv):
@@ -70,7 +76,7 @@ def blob_mesh(nu: int, nv: int, radius: float = 1.0, bump: float = 0.15, seed: i
         nz[-1, :] = nz[0, :]
         r = radius * (1.0 + bump * (nz - 1.0))
         return d * r[..., None] + np.asarray(center)[None, None, :], d
-    return grid_mesh(nu, nv, fn)
+    return grid_mesh(nu, nv, fn, indexed=indexed)
 
 
 def teapot_like_mesh(n: int = 56, seed: int = 7):
@@ -257,13 +263,18 @@ def cornell_smoke_scene(light_strength: float = 7.0, glass_sphere: bool = False)
     return sd, cam, dict(name="cornell_smoke", width=1024, height=1024, spp=4096)
 
 
-def big_mesh_scene(cache_dir: str, quads: int = 2290, env_w: int = 1024, env_h: int = 512):
-    """C5: one noise-displaced sphere with 2*quads^2 triangles (10,488,200 at quads=2290), metal 0.2, env-lit, 3840x2160."""
+def big_mesh_scene(cache_dir: str, quads: int = 2290, env_w: int = 1024, env_h: int = 512, indexed: bool = False):
+    """C5: one noise-displaced sphere with 2*quads^2 triangles (10,488,200 at quads=2290), metal 0.2, env-lit, 3840x2160.
+    indexed: the same triangles handed over as vertex / index buffers (hrt_scene_add_mesh_indexed)."""
     sd = SceneDesc()
     sd.background = env_texture(sd, cache_dir, env_w, env_h)
     shiny = sd.material(abi.MAT_METAL, (0.73, 0.73, 0.73), p0=0.2)
-    pos, nrm, uv = blob_mesh(quads, quads, radius=1.0, bump=0.2, seed=7, center=(0, 1, 0))
-    sd.add(sd.mesh(pos, nrm, uv, shiny))
+    if indexed:
+        v, n, t, idx = blob_mesh(quads, quads, radius=1.0, bump=0.2, seed=7, center=(0, 1, 0), indexed=True)
+        sd.add(sd.mesh_indexed(v, n, t, idx, shiny)); sd.borrow = True       # the arrays stay in sd.shapes: no copy at add time
+    else:
+        pos, nrm, uv = blob_mesh(quads, quads, radius=1.0, bump=0.2, seed=7, center=(0, 1, 0))
+        sd.add(sd.mesh(pos, nrm, uv, shiny))
     cam = dict(position=(0, 1, 3), look_at=(0, 1, 0), up=(0, 1, 0), vfov_deg=60, aperture=0.0, focal_distance=8.5)
     return sd, cam, dict(name="big_mesh", width=3840, height=2160, spp=64)
 

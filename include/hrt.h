@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define HRT_ABI_VERSION 4
+#define HRT_ABI_VERSION 5
 
 /* ---- error codes --------------------------------------------------------------------------- */
 #define HRT_OK            0
@@ -131,6 +131,8 @@ typedef struct hrt_stats {
                                  reference's sequential process over the collected candidates (HRT_BVH_SAH only) */
     uint64_t scene_bytes;     /* bytes of scene data resident in device memory after hrt_scene_commit  */
     double   ms_build;        /* time of the BVH builds in hrt_scene_commit (host builders, or upload + device build)   */
+    uint64_t h2d_bytes;       /* bytes hrt_scene_commit copied host -> device (scene arrays + mesh sources of device builds) */
+    double   ms_build_upload; /* HRT_BVH_LBVH_GPU: the part of ms_build spent copying mesh sources to the device       */
 } hrt_stats;
 
 typedef struct hrt_scene hrt_scene;
@@ -158,6 +160,29 @@ int hrt_scene_add_rect(hrt_scene* s, int axis, float a0, float a1, float b0, flo
 int hrt_scene_add_box(hrt_scene* s, const float center[3], const float dimensions[3], int material); /* box.h:41-44; 6 prims in box.h:31-38 order */
 int hrt_scene_add_mesh(hrt_scene* s, const float* positions /* n_tri*9 */, const float* normals /* n_tri*9 or NULL */,
                        const float* uvs /* n_tri*6 or NULL */, int64_t n_tri, int material);       /* mesh.cpp:13-41: one ITriangle per face + BVH */
+/* Mesh ingest fast path: the vertex / index buffers as Mesh::assimpLoadFile concatenates them over the file's aiMeshes
+ * (mesh.cpp:63-115), flattened by the library instead of by the caller - Mesh::Mesh's loop (mesh.cpp:24-33): triangle k
+ * takes vertices[indices[3k]], [3k+1], [3k+2] together with their normals and uvs (zeros when the file has none,
+ * mesh.cpp:87-99).  With HRT_BVH_LBVH_GPU the compact buffers are what crosses PCIe and the gather runs on the device.
+ * submeshes == NULL: indices are used as they are - the reference's behaviour, including its missing base-vertex offset
+ * for files with several aiMeshes (mesh.cpp:111-114).  With a table (one entry per aiMesh) index j of sub-mesh m is
+ * indices[first_index + j] + base_vertex: the corrected behaviour.  n_indices must be a multiple of 3 and every resolved
+ * index < n_vertices (the reference reads out of bounds there; this library returns HRT_ERR_ARG).
+ * The primitive ids, arrays and images are identical to hrt_scene_add_mesh on the flattened triangles.
+ * Without HRT_MESH_BORROW the arrays are copied and may be freed as soon as the call returns.                             */
+typedef struct hrt_submesh {
+    int64_t first_index;   /* position of the sub-mesh's first index in `indices`             */
+    int64_t n_index;       /* 3 * mNumFaces                                                    */
+    int64_t base_vertex;   /* position of the sub-mesh's first vertex in `vertices`            */
+} hrt_submesh;
+int hrt_scene_add_mesh_indexed(hrt_scene* s, const float* vertices /* n_vertices*3 */, const float* normals /* n_vertices*3 or NULL */,
+                               const float* uvs /* n_vertices*2 or NULL */, int64_t n_vertices,
+                               const uint32_t* indices, int64_t n_indices,
+                               const hrt_submesh* submeshes /* or NULL */, int n_submeshes, int material, uint32_t flags);
+#define HRT_MESH_BORROW 1u   /* the caller keeps vertices / normals / uvs (and, without a sub-mesh table, indices) alive and unchanged
+                                until hrt_scene_commit has returned; the library reads them in place instead of copying them at add
+                                time (ownership rule of Scene's vectors: they outlive the load, mesh.cpp:15-21).  After the commit
+                                the library no longer touches them. */
 int64_t hrt_scene_prim_base(const hrt_scene* s, int shape);
 int64_t hrt_scene_prim_count(const hrt_scene* s);
 

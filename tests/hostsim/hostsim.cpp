@@ -55,6 +55,8 @@ int hsim_scene_add_sphere(hsim_scene* s, const float c[3], float r, int m) { B(b
 int hsim_scene_add_rect(hsim_scene* s, int axis, float a0, float a1, float b0, float b1, float k, int m) { B(b_add_rect(s->host, axis, a0, a1, b0, b1, k, m, g_err)); }
 int hsim_scene_add_box(hsim_scene* s, const float c[3], const float d[3], int m) { B(b_add_box(s->host, c, d, m, g_err)); }
 int hsim_scene_add_mesh(hsim_scene* s, const float* p, const float* n, const float* uv, int64_t nt, int m) { B(b_add_mesh(s->host, p, n, uv, nt, m, g_err)); }
+int hsim_scene_add_mesh_indexed(hsim_scene* s, const float* v, const float* n, const float* uv, int64_t nv, const uint32_t* idx, int64_t ni,
+                                const hrt_submesh* sub, int n_sub, int m, uint32_t flags) { B(b_add_mesh_indexed(s->host, v, n, uv, nv, idx, ni, sub, n_sub, m, flags, g_err)); }
 int64_t hsim_scene_prim_base(const hsim_scene* s, int shape) { return s->host.shapes[(size_t)shape].prim_base; }
 int64_t hsim_scene_prim_count(const hsim_scene* s) { return s->host.n_prims; }
 int hsim_scene_add_object(hsim_scene* s, int shape, const hrt_xform* ops, int n) { B(b_add_object(s->host, shape, ops, n, g_err)); }
@@ -67,6 +69,7 @@ int hsim_scene_commit(hsim_scene* s, int bvh_mode, uint64_t seed)
     std::string e = flatten(s->host, bvh_mode, seed);
     if (!e.empty()) { g_err = e; return HRT_ERR_ARG; }
     s->d = make_dscene(s->host, s->up);
+    for (HostShape& sh : s->host.shapes) sh.release_borrowed();
     s->host.committed = true;
     return 0;
 }

@@ -108,3 +108,57 @@ def test_two_million_triangles(hrt):
     assert (rg["prim"] != abi.MISS).mean() > 0.3
     same = (rg["prim"] == rs["prim"]) & (bits(rg["t"]) == bits(rs["t"]))
     assert same.mean() > 0.9999, f"{(~same).sum()} rays differ between the stable-order and the std::sort topology"
+
+
+# ---- hrt_scene_add_mesh_indexed: the gather of mesh.cpp:24-33 done by the device builder (k_mesh_pack<true>) ----------
+def indexed_scene(v, n, t, idx, sub=None, flatten=False, borrow=False):
+    sd = abi.SceneDesc(); sd.flatten_for_all = flatten; sd.borrow = borrow
+    m = sd.material(abi.MAT_LAMBERTIAN, (0.5, 0.5, 0.5))
+    sd.add(sd.mesh_indexed(v, n, t, idx, m, sub))
+    return sd
+
+
+@pytest.mark.parametrize("mode", [abi.BVH_LBVH_GPU, abi.BVH_SAH, abi.BVH_REFERENCE])
+def test_indexed_mesh_arrays_equal_flattened_mesh(hrt, mode):
+    v, n, t, idx = scenes.blob_mesh(40, 40, 1.0, 0.2, seed=7, center=(0, 1, 0), indexed=True)
+    a = indexed_scene(v, n, t, idx).build(hrt, mode, 5)
+    b = indexed_scene(v, n, t, idx, flatten=True).build(hrt, mode, 5)
+    if mode == abi.BVH_REFERENCE:
+        for which in (0, 3, 4):
+            assert np.array_equal(a.mesh_array(0, which).view(np.uint32), b.mesh_array(0, which).view(np.uint32))
+    else:
+        same_arrays(a, b)
+    if mode == abi.BVH_LBVH_GPU:
+        same_arrays(a, indexed_scene(v, n, t, idx).build(hrt, abi.BVH_LBVH_HOST, 5))
+        assert a.stats().h2d_bytes < 0.5 * b.stats().h2d_bytes          # only the compact buffers cross PCIe
+
+
+def test_indexed_mesh_hits_bit_exact_with_oracle(orc, hrt):
+    va, na, ta, ia = scenes.blob_mesh(30, 30, 0.6, 0.2, seed=1, center=(-0.8, 1, 0), indexed=True)
+    vb, nb, tb, ib = scenes.blob_mesh(20, 34, 0.5, 0.2, seed=2, center=(0.9, 1, 0), indexed=True)
+    v = np.concatenate([va, vb]); n = np.concatenate([na, nb]); t = np.concatenate([ta, tb]); idx = np.concatenate([ia, ib])
+    sub = [(0, ia.shape[0], 0), (ia.shape[0], ib.shape[0], va.shape[0])]
+    rays = scenes.random_rays(200000, (0, 1, 0), 2.5, seed=8)
+    for table in (sub, None):                       # corrected base-vertex offset / the reference's as-is indexing (mesh.cpp:111-114)
+        sd = indexed_scene(v, n, t, idx, table)
+        o = sd.build(orc, abi.BVH_LBVH_GPU, 5); g = sd.build(hrt, abi.BVH_LBVH_GPU, 5)
+        ro = o.trace(rays)
+        assert (ro["prim"] != abi.MISS).mean() > 0.02
+        check(ro, g.trace(rays), front=False)
+        check(sd.build(orc, abi.BVH_REFERENCE, 5).trace(rays), sd.build(hrt, abi.BVH_SAH, 5).trace(rays), front=False)
+
+
+def test_indexed_two_million_triangles(hrt):
+    v, n, t, idx = scenes.blob_mesh(1000, 1000, 1.0, 0.15, seed=7, indexed=True)
+    a = indexed_scene(v, n, t, idx).build(hrt, abi.BVH_LBVH_GPU, 3)
+    b = indexed_scene(v, n, t, idx, flatten=True).build(hrt, abi.BVH_LBVH_GPU, 3)
+    same_arrays(a, b)
+    vv, nn, tt, ii = v.copy(), n.copy(), t.copy(), idx.copy()
+    c = indexed_scene(vv, nn, tt, ii, borrow=True).build(hrt, abi.BVH_LBVH_GPU, 3)      # HRT_MESH_BORROW: read in place until the commit returns
+    vv[:] = np.nan; ii[:] = 0xFFFFFFFF
+    same_arrays(a, c)
+    sa, sb = a.stats(), b.stats()
+    assert sa.h2d_bytes < 0.35 * sb.h2d_bytes, f"{sa.h2d_bytes} vs {sb.h2d_bytes} bytes host -> device"
+    rays = scenes.random_rays(1 << 18, (0, 0, 0), 1.5, seed=8)
+    ra, rb = a.trace(rays, extras=False), b.trace(rays, extras=False)
+    assert np.array_equal(ra["prim"], rb["prim"]) and np.array_equal(bits(ra["t"]), bits(rb["t"]))

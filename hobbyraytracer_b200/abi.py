@@ -25,6 +25,9 @@ RENDER_WAVEFRONT_V1 = 2
 MESH_BORROW = 1
 
 
+PROGRESS_FN = C.CFUNCTYPE(C.c_int, C.c_int, C.c_int, C.c_void_p)      # hrt_progress_fn
+
+
 class Material(C.Structure):
     _fields_ = [("kind", C.c_int32), ("albedo", C.c_float * 3), ("albedo_tex", C.c_int32),
                 ("p0", C.c_float), ("p0_tex", C.c_int32), ("p1", C.c_float), ("p1_tex", C.c_int32)]
@@ -126,6 +129,8 @@ class Lib:
         self._sig("device_count", i, [], required=False)
         self._sig("set_device", i, [i], required=False)
         self._sig("render", i, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp], required=False)
+        self._sig("render_progressive", i, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), C.c_char_p, i, PROGRESS_FN, _vp, _vp, _vp], required=False)
+        self._sig("checkpoint_samples", i, [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)], required=False)
         self._sig("render_accumulate_device", i, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp], required=False)
         self._sig("film_resolve_device", i, [_vp, _vp, i, i, i, _vp, _vp, _vp, _vp], required=False)
         self._sig("film_bytes", i, [i, i], required=False)
@@ -356,6 +361,17 @@ class Scene:
         b = np.empty((height, width, 3), np.uint8) if want_rgb8 else None
         self.lib.check(self.lib.fn("render")(self.h, C.byref(cam), C.byref(p), _ptr(s), _ptr(b)), "render")
         return s, b
+
+    def render_progressive(self, cam: Camera, width: int, height: int, spp: int, seed: int = 1, checkpoint: Optional[str] = None,
+                           slice_spp: int = 0, on_slice=None, max_depth: int = 50, t_min: float = 0.001, rng_mode: int = 0, flags: int = 0):
+        """hrt_render_progressive -> (rc, sum, rgb8); rc 1 = stopped by on_slice(samples_done, spp) returning non-zero."""
+        p = RenderParams(width, height, spp, 0, 0, max_depth, t_min, seed, rng_mode, flags)
+        s = np.empty((height, width, 3), np.float32); b = np.empty((height, width, 3), np.uint8)
+        cb = PROGRESS_FN(lambda done, total, user: int(on_slice(done, total) or 0)) if on_slice else PROGRESS_FN(0)
+        rc = self.lib.fn("render_progressive")(self.h, C.byref(cam), C.byref(p), checkpoint.encode() if checkpoint else None,
+                                               slice_spp, cb, None, _ptr(s), _ptr(b))
+        self.lib.check(rc, "render_progressive")
+        return rc, s, b
 
     def mesh_array(self, mesh_index: int, which: int) -> np.ndarray:
         """One per-mesh array of the committed scene as float32 words (hrt_scene_mesh_array): 0 reference-topology nodes,

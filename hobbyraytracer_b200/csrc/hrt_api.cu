@@ -460,6 +460,118 @@ int hrt_render(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, 
     return 0;
 }
 
+// ---- checkpoints (hrt_render_progressive) ------------------------------------------------------------------------
+namespace {
+struct CheckpointHeader {
+    char     magic[8];            // "HRTFILM1"
+    int32_t  width, height, spp, samples_done, max_depth, rng_mode, flags_reserved;
+    float    t_min;
+    uint64_t seed, camera_hash, prim_count;
+};
+const char kCheckpointMagic[8] = {'H', 'R', 'T', 'F', 'I', 'L', 'M', '1'};
+uint64_t fnv1a(const void* p, size_t n) { const unsigned char* b = (const unsigned char*)p; uint64_t h = 1469598103934665603ull; for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; } return h; }
+CheckpointHeader checkpoint_header_of(const hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p)
+{
+    CheckpointHeader h; memset(&h, 0, sizeof(h));
+    memcpy(h.magic, kCheckpointMagic, 8);
+    h.width = p->width; h.height = p->height; h.spp = p->spp; h.samples_done = 0;
+    h.max_depth = p->max_depth > 0 ? p->max_depth : 50; h.rng_mode = p->rng_mode;
+    h.t_min = p->t_min > 0 ? p->t_min : 0.001f;
+    h.seed = p->seed; h.camera_hash = fnv1a(cam, sizeof(*cam)); h.prim_count = (uint64_t)s->host.n_prims;
+    return h;
+}
+bool same_render(const CheckpointHeader& a, const CheckpointHeader& b)
+{
+    return memcmp(a.magic, b.magic, 8) == 0 && a.width == b.width && a.height == b.height && a.spp == b.spp && a.max_depth == b.max_depth &&
+           a.rng_mode == b.rng_mode && memcmp(&a.t_min, &b.t_min, 4) == 0 && a.seed == b.seed && a.camera_hash == b.camera_hash && a.prim_count == b.prim_count;
+}
+int read_header(const char* path, CheckpointHeader& h, FILE** keep_open)
+{
+    FILE* f = fopen(path, "rb");
+    if (!f) return 1;                                                     // no such file: a fresh render
+    if (fread(&h, sizeof(h), 1, f) != 1 || memcmp(h.magic, kCheckpointMagic, 8) != 0) { fclose(f); g_err = std::string("not a checkpoint file: ") + path; return HRT_ERR_IO; }
+    if (keep_open) *keep_open = f; else fclose(f);
+    return 0;
+}
+int write_checkpoint(const char* path, const CheckpointHeader& h, const void* film, size_t bytes)
+{
+    const std::string tmp = std::string(path) + ".tmp";
+    FILE* f = fopen(tmp.c_str(), "wb");
+    if (!f) { g_err = "cannot write checkpoint " + tmp; return HRT_ERR_IO; }
+    const bool ok = fwrite(&h, sizeof(h), 1, f) == 1 && fwrite(film, 1, bytes, f) == bytes;
+    if (fclose(f) != 0 || !ok) { remove(tmp.c_str()); g_err = "short write on checkpoint " + tmp; return HRT_ERR_IO; }
+    if (rename(tmp.c_str(), path) != 0) { remove(tmp.c_str()); g_err = std::string("cannot move the checkpoint to ") + path; return HRT_ERR_IO; }
+    return 0;
+}
+} // namespace
+
+int hrt_checkpoint_samples(const char* path, int* width, int* height, int* spp)
+{
+    if (!path) { g_err = "path is NULL"; return HRT_ERR_ARG; }
+    CheckpointHeader h; int rc = read_header(path, h, nullptr);
+    if (rc == 1) { g_err = std::string("no such checkpoint: ") + path; return HRT_ERR_IO; }
+    if (rc < 0) return rc;
+    if (width) *width = h.width; if (height) *height = h.height; if (spp) *spp = h.spp;
+    return h.samples_done;
+}
+
+int hrt_render_progressive(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, const char* checkpoint_path,
+                           int slice_spp, hrt_progress_fn on_slice, void* user, float* out_sum, uint8_t* out_rgb8)
+{
+    int rc = check_render_args(s, cam, p); if (rc < 0) return rc;
+    if (p->sample_first != 0 || (p->sample_count > 0 && p->sample_count != p->spp)) { g_err = "a progressive render covers all samples"; return HRT_ERR_ARG; }
+    CK(cudaSetDevice(s->device));
+    const size_t npix = (size_t)p->width * p->height;
+    const size_t film_bytes = sizeof(long long) * FILM_LANES * npix;
+    if (s->film_pixels < npix) {
+        cudaFree(s->d_film); s->d_film = nullptr; s->film_pixels = 0;
+        cudaFree(s->d_out); s->d_out = nullptr;
+        CK(cudaMalloc(&s->d_film, film_bytes));
+        CK(cudaMalloc(&s->d_out, sizeof(float) * npix * 3 + npix * 3));
+        s->film_pixels = npix;
+    }
+    cudaStream_t st = s->stream;
+    CheckpointHeader head = checkpoint_header_of(s, cam, p);
+    std::vector<unsigned char> host_film;
+    if (checkpoint_path) host_film.resize(film_bytes);
+    bool resumed = false;
+    if (checkpoint_path) {
+        CheckpointHeader on_disk; FILE* f = nullptr;
+        rc = read_header(checkpoint_path, on_disk, &f);
+        if (rc < 0) return rc;
+        if (rc == 0) {
+            const bool ok = same_render(head, on_disk) && on_disk.samples_done >= 0 && on_disk.samples_done <= p->spp;
+            const bool full = ok && fread(host_film.data(), 1, film_bytes, f) == film_bytes;
+            fclose(f);
+            if (!ok) { g_err = std::string("checkpoint belongs to a different render: ") + checkpoint_path; return HRT_ERR_IO; }
+            if (!full) { g_err = std::string("checkpoint is truncated: ") + checkpoint_path; return HRT_ERR_IO; }
+            head.samples_done = on_disk.samples_done; resumed = true;
+            CK(cudaMemcpyAsync(s->d_film, host_film.data(), film_bytes, cudaMemcpyHostToDevice, st));
+        }
+    }
+    if (!resumed) CK(cudaMemsetAsync(s->d_film, 0, film_bytes, st));
+    const int slice = slice_spp > 0 ? slice_spp : p->spp;
+    while (head.samples_done < p->spp) {
+        hrt_render_params q = *p;
+        q.sample_first = head.samples_done; q.sample_count = std::min(slice, p->spp - head.samples_done);
+        rc = render_into(s, cam, &q, s->d_film, st); if (rc < 0) return rc;
+        head.samples_done += q.sample_count;
+        if (checkpoint_path) {
+            CK(cudaMemcpyAsync(host_film.data(), s->d_film, film_bytes, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            rc = write_checkpoint(checkpoint_path, head, host_film.data(), film_bytes); if (rc < 0) return rc;
+        } else if (on_slice) CK(cudaStreamSynchronize(st));
+        if (on_slice && on_slice(head.samples_done, p->spp, user) != 0 && head.samples_done < p->spp) { CK(cudaStreamSynchronize(st)); return HRT_STOPPED; }
+    }
+    uint8_t* d_rgb8 = (uint8_t*)(s->d_out + npix * 3);
+    launch_film_resolve(s->d_film, (int)npix, p->spp, out_sum ? s->d_out : nullptr, nullptr, out_rgb8 ? d_rgb8 : nullptr, s->sm_count, st, &s->stats.launches);
+    if (out_sum) CK(cudaMemcpyAsync(out_sum, s->d_out, sizeof(float) * npix * 3, cudaMemcpyDeviceToHost, st));
+    if (out_rgb8) CK(cudaMemcpyAsync(out_rgb8, d_rgb8, npix * 3, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    return 0;
+}
+
 void* hrt_film_create(int width, int height)
 {
     const int bytes = hrt_film_bytes(width, height);

@@ -213,6 +213,23 @@ int hrt_trace_batch_device(hrt_scene* s, const void* d_rays, int64_t n, void* d_
  * samples (NULL to skip); out_rgb8: width*height*3 bytes = Film::tonemap + writeColour of sum/spp
  * (film.cpp:25-52), row 0 = top row as in the reference's pixel buffer (NULL to skip). */
 int hrt_render(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, float* out_sum, uint8_t* out_rgb8);
+/* render() in slices, with checkpoints and the reference's progress reporting (main.cpp:95-109 prints "Pixels rendered"
+ * from a reporter thread; here the caller gets a callback after every slice).  The p->spp samples of every pixel are
+ * rendered slice_spp at a time (<= 0: one slice).  checkpoint_path != NULL: after every slice the integer film is written
+ * there (temporary file + rename) together with the render parameters; when the file already exists and belongs to the same
+ * render (size, spp, seed, rng mode, depth, t_min, camera, primitive count) rendering RESUMES after the samples it holds,
+ * and a file from a different render is HRT_ERR_IO, never silently overwritten.  The film is integer and Philox is keyed
+ * by the sample index, so the image is bit-identical to hrt_render's for any slicing and any number of interruptions.
+ * on_slice (may be NULL) is called on the calling thread with the samples finished so far; returning non-zero stops the
+ * render: the call returns HRT_STOPPED (1) with the checkpoint kept and no image written.  p->sample_first/sample_count
+ * must select the whole image (0 / <= 0 or spp).                                                                        */
+#define HRT_STOPPED 1
+typedef int (*hrt_progress_fn)(int samples_done, int spp, void* user);
+int hrt_render_progressive(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, const char* checkpoint_path,
+                           int slice_spp, hrt_progress_fn on_slice, void* user, float* out_sum, uint8_t* out_rgb8);
+/* The checkpoint file on its own (tooling): samples held by a checkpoint, or HRT_ERR_IO.                                 */
+int hrt_checkpoint_samples(const char* checkpoint_path, int* width, int* height, int* spp);
+
 /* Device variants for multi-GPU use.  The FILM is a device buffer of hrt_film_bytes(width, height) bytes:
  * per pixel four int64 lanes — the r, g, b sample sums in fixed point (2^-26 units; every sample rounded to
  * nearest and clamped to +-2^21) and one lane of "a NaN / +inf / -inf sample was added" fields.  Integer sums

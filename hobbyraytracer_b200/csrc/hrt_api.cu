@@ -305,8 +305,7 @@ int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed)
     NEED(s);
     if (bvh_mode < HRT_BVH_REFERENCE || bvh_mode > HRT_BVH_LBVH_HOST) { g_err = "unknown bvh mode"; return HRT_ERR_ARG; }
     CK(cudaSetDevice(s->device));
-    cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, s->device));
-    s->sm_count = prop.multiProcessorCount;
+    CK(cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, s->device));   // (cudaGetDeviceProperties costs ~1 ms per commit)
     std::string e = flatten(s->host, bvh_mode, seed);
     if (!e.empty()) { g_err = e; return HRT_ERR_ARG; }
     CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));

@@ -22,6 +22,7 @@ XF_TRANSLATE, XF_SCALE, XF_ROTATE_QUAT, XF_ROTATE_Y, XF_ROTATE_EULER_DEG, XF_ROT
 BVH_REFERENCE, BVH_SAH, BVH_LBVH_GPU, BVH_LBVH_HOST = range(4)
 RENDER_MEGAKERNEL = 1
 RENDER_WAVEFRONT_V1 = 2
+RENDER_DEFOCUS = 4
 MESH_BORROW = 1
 
 
@@ -144,6 +145,7 @@ class Lib:
         # oracle-only
         self._sig("render_u8", i, [_vp, C.POINTER(Camera), i, i, i, u64, _vp], required=False)
         self._sig("render_f32", i, [_vp, C.POINTER(Camera), i, i, i, u64, i, _vp, _vp], required=False)
+        self._sig("render_f32_defocus", i, [_vp, C.POINTER(Camera), i, i, i, u64, i, _vp, _vp], required=False)
         self._sig("film_resolve", i, [_vp, i, i, i, _vp], required=False)
         self._sig("camera_rays", i, [C.POINTER(Camera), _vp, i64, _vp], required=False)
         self._sig("rng_draw", i, [i, u64, u64, i64, _vp], required=False)
@@ -396,6 +398,11 @@ class Scene:
     def render_f32(self, cam: Camera, width: int, height: int, spp: int, seed: int = 1, threads: int = 0):
         s = np.empty((height, width, 3), np.float32); rays = C.c_uint64(0)
         self.lib.check(self.lib.fn("render_f32")(self.h, C.byref(cam), width, height, spp, seed, threads, _ptr(s), C.byref(rays)), "render_f32")
+        return s, int(rays.value)
+
+    def render_f32_defocus(self, cam: Camera, width: int, height: int, spp: int, seed: int = 1, threads: int = 0):
+        s = np.empty((height, width, 3), np.float32); rays = C.c_uint64(0)
+        self.lib.check(self.lib.fn("render_f32_defocus")(self.h, C.byref(cam), width, height, spp, seed, threads, _ptr(s), C.byref(rays)), "render_f32_defocus")
         return s, int(rays.value)
 
     def scatter(self, material: int, inputs: np.ndarray, front: np.ndarray, seed: int = 0) -> np.ndarray:

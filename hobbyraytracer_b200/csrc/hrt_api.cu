@@ -164,7 +164,8 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
     j.tiles_x = tiled ? p->width / 8 : 0; j.tiles_y = tiled ? p->height / 4 : 0;
     j.t_min = p->t_min > 0 ? p->t_min : 0.001f; j.seed = p->seed; j.rng_mode = p->rng_mode;
     j.s_first = first; j.s_count = count; j.capacity = (unsigned int)cap; j.film = d_film;
-    const DCamera dc = make_camera(*cam);
+    DCamera dc = make_camera(*cam);
+    if ((p->flags & HRT_RENDER_DEFOCUS) && cam->aperture > 0.0f) dc.lens_radius = cam->aperture / 2.0f;   // camera.h:29
 
     constexpr int CHUNK = 8;                              // iterations between two looks at the control block
     constexpr int EV_PER_CHUNK = 2 * CHUNK + 2;           // per iteration: before trace, before shade; + chunk end + snapshot
@@ -474,7 +475,7 @@ CheckpointHeader checkpoint_header_of(const hrt_scene* s, const hrt_camera* cam,
     CheckpointHeader h; memset(&h, 0, sizeof(h));
     memcpy(h.magic, kCheckpointMagic, 8);
     h.width = p->width; h.height = p->height; h.spp = p->spp; h.samples_done = 0;
-    h.max_depth = p->max_depth > 0 ? p->max_depth : 50; h.rng_mode = p->rng_mode;
+    h.max_depth = p->max_depth > 0 ? p->max_depth : 50; h.rng_mode = p->rng_mode; h.flags_reserved = p->flags & HRT_RENDER_DEFOCUS;
     h.t_min = p->t_min > 0 ? p->t_min : 0.001f;
     h.seed = p->seed; h.camera_hash = fnv1a(cam, sizeof(*cam)); h.prim_count = (uint64_t)s->host.n_prims;
     return h;
@@ -482,7 +483,7 @@ CheckpointHeader checkpoint_header_of(const hrt_scene* s, const hrt_camera* cam,
 bool same_render(const CheckpointHeader& a, const CheckpointHeader& b)
 {
     return memcmp(a.magic, b.magic, 8) == 0 && a.width == b.width && a.height == b.height && a.spp == b.spp && a.max_depth == b.max_depth &&
-           a.rng_mode == b.rng_mode && memcmp(&a.t_min, &b.t_min, 4) == 0 && a.seed == b.seed && a.camera_hash == b.camera_hash && a.prim_count == b.prim_count;
+           a.rng_mode == b.rng_mode && a.flags_reserved == b.flags_reserved && memcmp(&a.t_min, &b.t_min, 4) == 0 && a.seed == b.seed && a.camera_hash == b.camera_hash && a.prim_count == b.prim_count;
 }
 int read_header(const char* path, CheckpointHeader& h, FILE** keep_open)
 {

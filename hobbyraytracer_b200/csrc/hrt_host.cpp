@@ -115,6 +115,8 @@ DCamera make_camera(const hrt_camera& c)                      // camera.h:9-30
     k.llc[0] = llc.x; k.llc[1] = llc.y; k.llc[2] = llc.z;
     k.horiz[0] = horiz.x; k.horiz[1] = horiz.y; k.horiz[2] = horiz.z;
     k.vert[0] = vert.x; k.vert[1] = vert.y; k.vert[2] = vert.z;
+    k.u[0] = u.x; k.u[1] = u.y; k.u[2] = u.z; k.v[0] = v.x; k.v[1] = v.y; k.v[2] = v.z;
+    k.lens_radius = 0.0f;                                       // the caller sets aperture / 2 under HRT_RENDER_DEFOCUS
     return k;
 }
 

@@ -428,7 +428,7 @@ __device__ __forceinline__ bool camera_ray_clears_scene(const DScene& s, const R
     return tn > tf || tf < fminf(t_min, 0.0f);
 }
 
-template <int MINB>
+template <int MINB, bool LENS>
 __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j, DCamera cam, int q, int skip_secondary)
 {
     WaveCtl* c = j.ctl;
@@ -482,7 +482,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j
             pix = c_pix;
             if (active) {
                 RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + c_sl), j.rng_mode);
-                r = primary_ray_xy(cam, j.width, j.height, c_x, j.height - c_y, key);
+                r = primary_ray_xy<LENS>(cam, j.width, j.height, c_x, j.height - c_y, key);
                 st = pack_state(c_sl, 0, false);
             }
             ++c_sl; --c_left;
@@ -648,8 +648,14 @@ void launch_wave2_trace(const DScene& s, const WaveJob& j, const DCamera& cam, i
     // teapot_scene 1199 / 997, but shiny_teapot 7194 / 7715 and the 2.9 M-triangle big mesh 2000 / 2144, whose secondary rays mostly leave at once)
     const int refill = s.refill_secondary && secondary_heavy;
     if (refill) { k_wave2_secondary<<<sm_count * HRT_DYN_MIN_BLOCKS, BLOCK, 0, st>>>(s, j, it & 1); *launches += 1; }
-    if (secondary_heavy) k_wave2_trace<8><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
-    else k_wave2_trace<4><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
+    const bool lens = cam.lens_radius > 0.0f;             // HRT_RENDER_DEFOCUS: the instantiation with the lens sampling compiled in
+    if (secondary_heavy) {
+        if (lens) k_wave2_trace<8, true><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
+        else k_wave2_trace<8, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
+    } else {
+        if (lens) k_wave2_trace<4, true><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
+        else k_wave2_trace<4, false><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
+    }
     *launches += 1;
 }
 void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches)

@@ -181,11 +181,21 @@ HRT_HDN inline bool shade_segment(const DScene& s, const Hit& h, Ray& r, V3& att
 }
 
 // ---- camera: getRay camera.h:32-39 (the lens offset is forced to zero there) ---------------------------------------------
-HRT_HD Ray camera_ray(const DCamera& c, float s, float t)
+// lens_word: a spare word of the camera-jitter draw, used only under HRT_RENDER_DEFOCUS (c.lens_radius > 0) for
+// glm::circularRand(lensRadius) (random.inl:281-287): a = linearRand(0, 2 pi), rd = (cos a, sin a) * Radius
+// LENS = false compiles the lens code out: the fused trace kernel is instantiated both ways and picked by the host, because
+// even the never-taken branch cost the headline 2.8 % (B200 A/B: 8287 -> 8054 Mrays/s, profiles/README.md r1m).
+template <bool LENS = true>
+HRT_HD Ray camera_ray(const DCamera& c, float s, float t, uint32_t lens_word = 0, int mode = 0)
 {
     V3 origin = v3(c.origin[0], c.origin[1], c.origin[2]), llc = v3(c.llc[0], c.llc[1], c.llc[2]);
     V3 horiz = v3(c.horiz[0], c.horiz[1], c.horiz[2]), vert = v3(c.vert[0], c.vert[1], c.vert[2]);
     V3 off = v3(0.0f);
+    if (LENS && c.lens_radius > 0.0f) {
+        const float a = linear_f(lens_word, mode, 0.0f, 6.283185307179586476925286766559f);
+        const float rx = cosf(a) * c.lens_radius, ry = sinf(a) * c.lens_radius;
+        off = v3(c.u[0], c.u[1], c.u[2]) * rx + v3(c.v[0], c.v[1], c.v[2]) * ry;    // camera.h:35
+    }
     Ray r; r.o = origin + off; r.d = llc + s * horiz + t * vert - origin - off;
     return r;
 }
@@ -196,16 +206,17 @@ HRT_HD Ray primary_ray(const DCamera& c, int w, int h, int pidx, const RngKey& k
     U4 j = rng_draw(key, BOUNCE_CAMERA, 0);
     float u = ((float)x + linear_f(j.x, key.mode, 0.0f, 1.0f)) / (w - 1);
     float v = ((float)y + linear_f(j.y, key.mode, 0.0f, 1.0f)) / (h - 1);
-    return camera_ray(c, u, v);
+    return camera_ray(c, u, v, j.z, key.mode);
 }
 
 // same ray from the pixel coordinates the caller already has (x = pIdx % W, y = H - pIdx / W, main.cpp:115-116)
+template <bool LENS = true>
 HRT_HD Ray primary_ray_xy(const DCamera& c, int w, int h, int x, int y, const RngKey& key)
 {
     U4 j = rng_draw(key, BOUNCE_CAMERA, 0);
     float u = ((float)x + linear_f(j.x, key.mode, 0.0f, 1.0f)) / (w - 1);
     float v = ((float)y + linear_f(j.y, key.mode, 0.0f, 1.0f)) / (h - 1);
-    return camera_ray(c, u, v);
+    return camera_ray<LENS>(c, u, v, j.z, key.mode);
 }
 
 // ---- Film::tonemap + writeColour film.cpp:25-52 -----------------------------------------------------------------------------

@@ -92,6 +92,7 @@ struct DScene {
     uint32_t nan_prim;          // primitive accepts it (all comparisons false), so the last one in reference order wins; -1: miss
 };
 
-struct DCamera { float origin[3], llc[3], horiz[3], vert[3]; };   // camera.h:9-30
+struct DCamera { float origin[3], llc[3], horiz[3], vert[3];      // camera.h:9-30
+                 float u[3], v[3], lens_radius; };                 // lens basis; lens_radius 0 unless HRT_RENDER_DEFOCUS (camera.h:29,34)
 
 } // namespace hrt

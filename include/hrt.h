@@ -116,6 +116,11 @@ typedef struct hrt_render_params {
 
 #define HRT_RENDER_MEGAKERNEL 1   /* one thread per path instead of the persistent wavefront (debug/validation) */
 #define HRT_RENDER_WAVEFRONT_V1 2  /* every camera ray goes through the queues (the r1b/r1c pipeline, kept for A/B runs) */
+#define HRT_RENDER_DEFOCUS 4       /* opt-in: the lens sampling camera.h:34 has commented out ("TODO: Add back in randomness"):
+                                      rd = glm::circularRand(lensRadius), offset = u*rd.x + v*rd.y, lensRadius = aperture/2
+                                      (camera.h:29).  Without the flag - and with aperture == 0 - the offset is zero like
+                                      the reference's; the lens draw uses a spare word of the camera-jitter Philox call,
+                                      so no other random number of the path changes. */
 
 typedef struct hrt_stats {
     uint64_t rays;            /* closest-hit queries issued (= world->hit calls of main.cpp:45)      */

@@ -587,7 +587,7 @@ V3 ray_colour(const orc_scene& s, Ray r, int max_depth, float t_min, Rng& rng, u
     return result;
 }
 
-struct Cam { V3 origin, llc, horiz, vert; };
+struct Cam { V3 origin, llc, horiz, vert, u, v; float lens_radius = 0.0f; };
 Cam make_camera(const hrt_camera* c)                                               // camera.h:9-30
 {
     V3 from = v3(c->position[0], c->position[1], c->position[2]), lookat = v3(c->look_at[0], c->look_at[1], c->look_at[2]);
@@ -604,11 +604,25 @@ Cam make_camera(const hrt_camera* c)                                            
     k.horiz = c->focal_distance * vw * u;
     k.vert = c->focal_distance * vh * v;
     k.llc = k.origin - k.horiz / 2.0f - k.vert / 2.0f - c->focal_distance * w;
+    k.u = u; k.v = v;                                                              // lens_radius stays 0: camera.h:34 zeroes rd
     return k;
 }
 inline Ray get_ray(const Cam& c, float s, float t)                                 // camera.h:32-39 (lens offset is zero)
 {
     V3 off = v3(0.0f);                                                             // u*rd.x + v*rd.y with rd = 0
+    return Ray{c.origin + off, c.llc + s * c.horiz + t * c.vert - c.origin - off};
+}
+// The variant camera.h:34 has commented out ("TODO: Add back in randomness"): rd = glm::circularRand(lensRadius)
+// (random.inl:281-287), drawn when getRay is called, i.e. after the two jitter draws of main.cpp:120-121.  Only reached
+// through orc_render_f32_defocus (the opt-in HRT_RENDER_DEFOCUS of the product); not reference behaviour.
+template <class R> inline Ray get_ray_defocus(const Cam& c, float s, float t, R& rng)
+{
+    V3 off = v3(0.0f);
+    if (c.lens_radius > 0.0f) {
+        float a = rng.linear(0.0f, 6.283185307179586476925286766559f);
+        float rx = std::cos(a) * c.lens_radius, ry = std::sin(a) * c.lens_radius;
+        off = c.u * rx + c.v * ry;
+    }
     return Ray{c.origin + off, c.llc + s * c.horiz + t * c.vert - c.origin - off};
 }
 
@@ -824,6 +838,32 @@ int orc_render_f32(orc_scene* s, const hrt_camera* cam, int w, int h, int spp, u
                 float u = ((float)x + rng.linear(0.0f, 1.0f)) / (w - 1);
                 float v = ((float)y + rng.linear(0.0f, 1.0f)) / (h - 1);
                 px = px + ray_colour(*s, get_ray(c, u, v), 50, 0.001f, rng, nr);
+            }
+            out_sum[pIdx * 3] = px.x; out_sum[pIdx * 3 + 1] = px.y; out_sum[pIdx * 3 + 2] = px.z;
+        }
+        rays += nr;
+    });
+    if (rays_out) *rays_out = rays.load();
+    return 0;
+}
+
+// orc_render_f32 with the lens sampling of get_ray_defocus (lensRadius = aperture / 2, camera.h:29)
+int orc_render_f32_defocus(orc_scene* s, const hrt_camera* cam, int w, int h, int spp, uint64_t seed, int n_threads,
+                           float* out_sum, uint64_t* rays_out)
+{
+    if (!s->committed) { g_err = "scene not committed"; return HRT_ERR_STATE; }
+    Cam c = make_camera(cam);
+    if (cam->aperture > 0.0f) c.lens_radius = cam->aperture / 2.0f;
+    std::atomic<unsigned long long> rays(0);
+    parallel_rows(h, n_threads, [&](int row) {
+        Rng rng; rng.seed(seed, (uint64_t)row + 1); uint64_t nr = 0;
+        for (int xx = 0; xx < w; ++xx) {
+            int pIdx = row * w + xx; int x = pIdx % w; int y = h - pIdx / w;
+            V3 px = v3(0.0f);
+            for (int sidx = 0; sidx < spp; ++sidx) {
+                float u = ((float)x + rng.linear(0.0f, 1.0f)) / (w - 1);
+                float v = ((float)y + rng.linear(0.0f, 1.0f)) / (h - 1);
+                px = px + ray_colour(*s, get_ray_defocus(c, u, v, rng), 50, 0.001f, rng, nr);
             }
             out_sum[pIdx * 3] = px.x; out_sum[pIdx * 3 + 1] = px.y; out_sum[pIdx * 3 + 2] = px.z;
         }

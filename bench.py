@@ -266,7 +266,7 @@ def run_own(args):
         return stt
 
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
-    e2e_step(); sync_all()
+    e2e_step(); e2e_step(); sync_all()                 # two untimed end-to-end steps: host allocator, page cache and driver pools settle
     t0 = time.perf_counter(); e2e_rays = 0.0; scene_bytes = 0
     for _ in range(e2e_steps):
         stt = e2e_step(); e2e_rays += float(stt.rays); scene_bytes = int(stt.h2d_bytes)
@@ -403,7 +403,7 @@ def main():
     ap.add_argument("--reduce", default="peer", choices=["peer", "nccl"], help="N > 1: how the rank films reach rank 0")
     ap.add_argument("--pipeline", default="fused", choices=["fused", "v1"], help="fused: camera paths traced in the trace pass, only hits are queued; v1: every ray queued")
     ap.add_argument("--seed", type=int, default=1)
-    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

@@ -127,6 +127,7 @@ class Lib:
         self._sig("trace_batch_device", i, [_vp, _vp, i64, _vp, _vp, u64, _vp], required=False)
         # product-only
         self._sig("abi_version", i, [], required=False)
+        self._sig("trim", None, [], required=False)
         self._sig("device_count", i, [], required=False)
         self._sig("set_device", i, [i], required=False)
         self._sig("render", i, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp], required=False)

@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <utility>
@@ -78,6 +79,33 @@ namespace {
 
 constexpr int CTL_RING = 4;
 
+// Work buffers of a destroyed scene are parked (one set per process) instead of freed: a host that builds a scene per frame
+// (bench.py's end-to-end step, any animation loop) otherwise pays cudaMalloc + cudaFree of ~670 MB of queues and film per
+// frame.  The contents are scratch: every render writes a buffer before it reads it.  hrt_trim() releases them.
+struct Parked {
+    int device = -1;
+    unsigned int job_capacity = 0; WaveJob job{};
+    size_t film_pixels = 0; long long* d_film = nullptr; float* d_out = nullptr;
+    WaveCtl* h_ctl = nullptr;
+};
+std::mutex g_park_mutex;
+Parked g_parked;
+
+void cuda_free_job(WaveJob& job)
+{
+    for (int q = 0; q < 2; ++q) { cudaFree(job.rays[q]); cudaFree(job.thr[q]); cudaFree(job.res[q]); }
+    cudaFree(job.hits); cudaFree(job.ctl);
+    job = WaveJob{};
+}
+void trim_parked_locked()
+{
+    if (g_parked.device < 0) return;
+    int cur = 0; cudaGetDevice(&cur); cudaSetDevice(g_parked.device);
+    cuda_free_job(g_parked.job); cudaFree(g_parked.d_film); cudaFree(g_parked.d_out);
+    if (g_parked.h_ctl) cudaFreeHost(g_parked.h_ctl);
+    g_parked = Parked(); cudaSetDevice(cur);
+}
+
 void free_job(hrt_scene* s)
 {
     for (int q = 0; q < 2; ++q) { cudaFree(s->job.rays[q]); cudaFree(s->job.thr[q]); cudaFree(s->job.res[q]); }
@@ -99,6 +127,15 @@ int ensure_job(hrt_scene* s, unsigned int capacity)
 {
     if (capacity <= s->job_capacity) return 0;
     free_job(s);
+    {
+        std::lock_guard<std::mutex> lock(g_park_mutex);
+        if (g_parked.device == s->device && g_parked.job_capacity >= capacity) {       // a parked set fits: take it
+            s->job = g_parked.job; s->job_capacity = g_parked.job_capacity;
+            g_parked.job = WaveJob{}; g_parked.job_capacity = 0;
+            if (!s->h_ctl) { s->h_ctl = g_parked.h_ctl; g_parked.h_ctl = nullptr; }
+        }
+    }
+    if (s->job_capacity >= capacity) { if (!s->h_ctl) CK(cudaMallocHost(&s->h_ctl, sizeof(WaveCtl) * CTL_RING)); return 0; }
     for (int q = 0; q < 2; ++q) {
         CK(cudaMalloc(&s->job.rays[q], sizeof(float4) * 2 * (size_t)capacity));
         CK(cudaMalloc(&s->job.thr[q], sizeof(float4) * (size_t)capacity));
@@ -108,6 +145,24 @@ int ensure_job(hrt_scene* s, unsigned int capacity)
     CK(cudaMalloc(&s->job.ctl, sizeof(WaveCtl)));
     if (!s->h_ctl) CK(cudaMallocHost(&s->h_ctl, sizeof(WaveCtl) * CTL_RING));
     s->job_capacity = capacity;
+    return 0;
+}
+int ensure_film(hrt_scene* s, size_t npix)
+{
+    if (s->film_pixels >= npix) return 0;
+    cudaFree(s->d_film); s->d_film = nullptr; s->film_pixels = 0;
+    cudaFree(s->d_out); s->d_out = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_park_mutex);
+        if (g_parked.device == s->device && g_parked.film_pixels >= npix) {
+            s->d_film = g_parked.d_film; s->d_out = g_parked.d_out; s->film_pixels = g_parked.film_pixels;
+            g_parked.d_film = nullptr; g_parked.d_out = nullptr; g_parked.film_pixels = 0;
+            return 0;
+        }
+    }
+    CK(cudaMalloc(&s->d_film, sizeof(long long) * FILM_LANES * npix));
+    CK(cudaMalloc(&s->d_out, sizeof(float) * npix * 3 + npix * 3));
+    s->film_pixels = npix;
     return 0;
 }
 int ensure_tb(hrt_scene* s, long long n, bool own_rays)
@@ -264,11 +319,32 @@ hrt_scene* hrt_scene_create(void)
     s->device = g_device;
     return s;
 }
+void hrt_trim(void)
+{
+    std::lock_guard<std::mutex> lock(g_park_mutex);
+    trim_parked_locked();
+}
 void hrt_scene_destroy(hrt_scene* s)
 {
     if (!s) return;
     if (s->host.committed || s->stream) {
         cudaSetDevice(s->device);
+        cudaDeviceSynchronize();                                   // nothing may still be using what gets parked
+        {
+            std::lock_guard<std::mutex> lock(g_park_mutex);
+            if (g_parked.device != s->device) trim_parked_locked();
+            g_parked.device = s->device;
+            if (s->job_capacity > g_parked.job_capacity) {          // keep the larger set
+                cuda_free_job(g_parked.job);
+                g_parked.job = s->job; g_parked.job_capacity = s->job_capacity; s->job = WaveJob{}; s->job_capacity = 0;
+            }
+            if (s->film_pixels > g_parked.film_pixels) {
+                cudaFree(g_parked.d_film); cudaFree(g_parked.d_out);
+                g_parked.d_film = s->d_film; g_parked.d_out = s->d_out; g_parked.film_pixels = s->film_pixels;
+                s->d_film = nullptr; s->d_out = nullptr; s->film_pixels = 0;
+            }
+            if (s->h_ctl && !g_parked.h_ctl) { g_parked.h_ctl = s->h_ctl; s->h_ctl = nullptr; }
+        }
         free_job(s); free_tb(s); free_scene_device(s);
         cudaFree(s->d_film); cudaFree(s->d_out); cudaFree(s->d_counter);
         if (s->h_ctl) cudaFreeHost(s->h_ctl);
@@ -441,13 +517,7 @@ int hrt_render(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, 
     int rc = check_render_args(s, cam, p); if (rc < 0) return rc;
     CK(cudaSetDevice(s->device));
     const size_t npix = (size_t)p->width * p->height;
-    if (s->film_pixels < npix) {
-        cudaFree(s->d_film); s->d_film = nullptr; s->film_pixels = 0;
-        cudaFree(s->d_out); s->d_out = nullptr;
-        CK(cudaMalloc(&s->d_film, sizeof(long long) * FILM_LANES * npix));
-        CK(cudaMalloc(&s->d_out, sizeof(float) * npix * 3 + npix * 3));
-        s->film_pixels = npix;
-    }
+    rc = ensure_film(s, npix); if (rc < 0) return rc;
     cudaStream_t st = s->stream;
     CK(cudaMemsetAsync(s->d_film, 0, sizeof(long long) * FILM_LANES * npix, st));
     rc = render_into(s, cam, p, s->d_film, st); if (rc < 0) return rc;
@@ -523,13 +593,7 @@ int hrt_render_progressive(hrt_scene* s, const hrt_camera* cam, const hrt_render
     CK(cudaSetDevice(s->device));
     const size_t npix = (size_t)p->width * p->height;
     const size_t film_bytes = sizeof(long long) * FILM_LANES * npix;
-    if (s->film_pixels < npix) {
-        cudaFree(s->d_film); s->d_film = nullptr; s->film_pixels = 0;
-        cudaFree(s->d_out); s->d_out = nullptr;
-        CK(cudaMalloc(&s->d_film, film_bytes));
-        CK(cudaMalloc(&s->d_out, sizeof(float) * npix * 3 + npix * 3));
-        s->film_pixels = npix;
-    }
+    rc = ensure_film(s, npix); if (rc < 0) return rc;
     cudaStream_t st = s->stream;
     CheckpointHeader head = checkpoint_header_of(s, cam, p);
     std::vector<unsigned char> host_film;

@@ -150,7 +150,9 @@ int         hrt_set_device(int device);          /* device used by scenes create
 
 /* ---- scene builder (one call per construction site of scene.cpp) ---------------------------- */
 hrt_scene*  hrt_scene_create(void);
-void        hrt_scene_destroy(hrt_scene* s);
+void        hrt_scene_destroy(hrt_scene* s);         /* parks the scene's device work buffers (ray queues, film) for the next
+                                                        scene of this process instead of freeing them                      */
+void        hrt_trim(void);                          /* frees what hrt_scene_destroy parked                                */
 
 int hrt_scene_add_texture_solid(hrt_scene* s, const float rgb[3]);                    /* texture.h:9-25    */
 int hrt_scene_add_texture_checker(hrt_scene* s, int even_tex, int odd_tex);          /* texture.cpp:17-28 */

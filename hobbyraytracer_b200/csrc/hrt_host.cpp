@@ -13,6 +13,8 @@
 #include <chrono>
 #include <cmath>
 #include <atomic>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <map>
@@ -568,6 +570,7 @@ void build_mesh_host(HostShape& sh, int bvh_mode, uint64_t seed, int shape_id, i
 {
     const bool fast = bvh_mode != HRT_BVH_REFERENCE;
     const bool lbvh = bvh_mode == HRT_BVH_LBVH_HOST || bvh_mode == HRT_BVH_LBVH_GPU;
+    const double t_enter = now_ms();
     ensure_soup(sh);
     double t0 = now_ms();
     build_ref_bvh(sh, seed, shape_id, nt, lbvh);
@@ -609,6 +612,8 @@ void build_mesh_host(HostShape& sh, int bvh_mode, uint64_t seed, int shape_id, i
         } else build_fast_bvh(bmin, bmax, sh.fast, nt);
         ms_fast += now_ms() - t0;
     }
+    if (getenv("HRT_DEBUG_BUILD")) fprintf(stderr, "[hrt] host build of shape %d: %lld triangles, total %.2f ms (reference topology so far %.2f, fast tree so far %.2f)\n",
+                                           shape_id, (long long)sh.n_tri, now_ms() - t_enter, ms_ref, ms_fast);
     sh.n_ref_nodes = sh.ref.nodes.size() / 2; sh.n_fast_nodes = sh.fast.nodes.size() / 4; sh.n_leaves = sh.leaves.size() / 8;
 }
 

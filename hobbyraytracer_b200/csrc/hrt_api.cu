@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <unordered_map>
 #include <string>
 #include <thread>
 #include <utility>
@@ -33,17 +34,49 @@ int g_device = 0;
         }                                                                                                 \
     } while (0)
 
+// Scene arrays of a destroyed scene are kept (by exact size, bounded) for the next commit of this process: a host that rebuilds
+// its scene every frame uploads into the same blocks instead of cudaMalloc / cudaFree of every array (hrt_trim frees them).
+struct BlockCache {
+    struct Block { int device; size_t bytes; void* p; };
+    std::mutex m; std::vector<Block> blocks; size_t total = 0;
+    static constexpr size_t MAX_TOTAL = size_t(1) << 30, MAX_BLOCKS = 256;
+    void* take(int device, size_t bytes)
+    {
+        std::lock_guard<std::mutex> lock(m);
+        for (size_t i = 0; i < blocks.size(); ++i)
+            if (blocks[i].device == device && blocks[i].bytes == bytes) { void* p = blocks[i].p; total -= bytes; blocks[i] = blocks.back(); blocks.pop_back(); return p; }
+        return nullptr;
+    }
+    void give(int device, size_t bytes, void* p)
+    {
+        {
+            std::lock_guard<std::mutex> lock(m);
+            if (blocks.size() < MAX_BLOCKS && total + bytes <= MAX_TOTAL) { blocks.push_back(Block{device, bytes, p}); total += bytes; return; }
+        }
+        cudaFree(p);
+    }
+    void trim()
+    {
+        std::lock_guard<std::mutex> lock(m);
+        int cur = 0; cudaGetDevice(&cur);
+        for (const Block& b : blocks) { cudaSetDevice(b.device); cudaFree(b.p); }
+        cudaSetDevice(cur); blocks.clear(); total = 0;
+    }
+};
+BlockCache g_blocks;
+
 struct DevUp {
-    std::vector<void*>& allocs; bool failed = false; std::string msg; size_t bytes = 0;
-    explicit DevUp(std::vector<void*>& a) : allocs(a) {}
+    std::vector<void*>& allocs; std::unordered_map<void*, size_t>& sizes; int device;
+    bool failed = false; std::string msg; size_t bytes = 0;
+    DevUp(std::vector<void*>& a, std::unordered_map<void*, size_t>& z, int dev) : allocs(a), sizes(z), device(dev) {}
     const void* put(const void* p, size_t n)
     {
         if (!n || failed) return nullptr;
-        void* d = nullptr;
-        cudaError_t e = cudaMalloc(&d, n);
+        void* d = g_blocks.take(device, n);
+        cudaError_t e = d ? cudaSuccess : cudaMalloc(&d, n);
         if (e == cudaSuccess) e = cudaMemcpy(d, p, n, cudaMemcpyHostToDevice);
         if (e != cudaSuccess) { failed = true; msg = cudaGetErrorString(e); if (d) cudaFree(d); return nullptr; }
-        allocs.push_back(d); bytes += n;
+        allocs.push_back(d); sizes[d] = n; bytes += n;
         return d;
     }
     const void* put_copy(const void* p, size_t n) { return put(p, n); }
@@ -56,6 +89,7 @@ struct hrt_scene {
     int device = 0, sm_count = 148;
     cudaStream_t stream = nullptr;
     std::vector<void*> scene_allocs;
+    std::unordered_map<void*, size_t> scene_alloc_bytes;        // sizes of the uploaded arrays (device-built ones are not listed)
     size_t scene_bytes = 0, h2d_bytes = 0; double ms_build_upload = 0;
     // persistent-wavefront working set
     WaveJob job{};
@@ -119,8 +153,11 @@ void free_tb(hrt_scene* s)
 }
 void free_scene_device(hrt_scene* s)
 {
-    for (void* p : s->scene_allocs) cudaFree(p);
-    s->scene_allocs.clear(); s->scene_bytes = 0;
+    for (void* p : s->scene_allocs) {
+        auto it = s->scene_alloc_bytes.find(p);
+        if (it != s->scene_alloc_bytes.end()) g_blocks.give(s->device, it->second, p); else cudaFree(p);
+    }
+    s->scene_allocs.clear(); s->scene_alloc_bytes.clear(); s->scene_bytes = 0;
 }
 
 int ensure_job(hrt_scene* s, unsigned int capacity)
@@ -321,8 +358,8 @@ hrt_scene* hrt_scene_create(void)
 }
 void hrt_trim(void)
 {
-    std::lock_guard<std::mutex> lock(g_park_mutex);
-    trim_parked_locked();
+    { std::lock_guard<std::mutex> lock(g_park_mutex); trim_parked_locked(); }
+    g_blocks.trim();
 }
 void hrt_scene_destroy(hrt_scene* s)
 {
@@ -412,7 +449,7 @@ int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed)
         if (getenv("HRT_DEBUG_BUILD")) fprintf(stderr, "[hrt] device build of shape %d: %lld triangles, source %.1f MB (%s) uploaded in %.1f ms, built in %.1f ms\n",
                                                shape, (long long)sh.n_tri, b.h2d_bytes / 1e6, sh.indexed ? "indexed" : "soup", b.ms_upload, b.ms_build);
     }
-    DevUp up(s->scene_allocs);
+    DevUp up(s->scene_allocs, s->scene_alloc_bytes, s->device);
     s->d = make_dscene(s->host, up);
     if (const char* e = getenv("HRT_REFILL_SECONDARY")) s->d.refill_secondary = (atoi(e) != 0 && s->d.fast) ? 1 : 0;   // A/B override
     if (up.failed) { g_err = "scene upload failed: " + up.msg; free_scene_device(s); return HRT_ERR_CUDA; }

@@ -101,6 +101,7 @@ struct hrt_scene {
     // ray-batch working set
     float4* tb_rays = nullptr; Hit* tb_hits = nullptr;
     uint32_t* tb_prim = nullptr; float* tb_t = nullptr; long long tb_capacity = 0;
+    unsigned int* tb_pend = nullptr;                            // tb_capacity indices + 1 count: rays left to pass 2
     unsigned long long* d_counter = nullptr;                    // ray hand-out counter of k_trace_batch
     hrt_stats stats{};
     bool last_secondary_heavy = false;
@@ -148,8 +149,8 @@ void free_job(hrt_scene* s)
 }
 void free_tb(hrt_scene* s)
 {
-    cudaFree(s->tb_rays); cudaFree(s->tb_hits); cudaFree(s->tb_prim); cudaFree(s->tb_t);
-    s->tb_rays = nullptr; s->tb_hits = nullptr; s->tb_prim = nullptr; s->tb_t = nullptr; s->tb_capacity = 0;
+    cudaFree(s->tb_rays); cudaFree(s->tb_hits); cudaFree(s->tb_prim); cudaFree(s->tb_t); cudaFree(s->tb_pend);
+    s->tb_pend = nullptr; s->tb_rays = nullptr; s->tb_hits = nullptr; s->tb_prim = nullptr; s->tb_t = nullptr; s->tb_capacity = 0;
 }
 void free_scene_device(hrt_scene* s)
 {
@@ -211,6 +212,7 @@ int ensure_tb(hrt_scene* s, long long n, bool own_rays)
         CK(cudaMalloc(&s->tb_hits, sizeof(Hit) * (size_t)n));
         CK(cudaMalloc(&s->tb_prim, sizeof(uint32_t) * (size_t)n));
         CK(cudaMalloc(&s->tb_t, sizeof(float) * (size_t)n));
+        CK(cudaMalloc(&s->tb_pend, sizeof(unsigned int) * ((size_t)n + 1)));
         s->tb_capacity = n;
     }
     (void)own_rays;
@@ -489,7 +491,7 @@ int hrt_trace_batch_device(hrt_scene* s, const void* d_rays, int64_t n, void* d_
     if (n > s->tb_capacity) {                      // only hits / retrace list are needed for a device call; allocate the full set for simplicity
         int rc = ensure_tb(s, n, false); if (rc < 0) return rc;
     }
-    launch_trace_batch(s->d, (const float4*)d_rays, n, s->tb_hits, rng_seed, s->d_counter, s->sm_count, st, &s->stats.launches);
+    launch_trace_batch(s->d, (const float4*)d_rays, n, s->tb_hits, rng_seed, s->d_counter, s->tb_pend, s->tb_pend + n, s->sm_count, st, &s->stats.launches);
     launch_split_hits(s->tb_hits, n, (uint32_t*)d_prim_id, (float*)d_t, s->sm_count, st, &s->stats.launches);
     CK(cudaGetLastError());
     s->stats.rays += (uint64_t)n;

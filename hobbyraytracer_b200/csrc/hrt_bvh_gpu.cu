@@ -144,7 +144,11 @@ __global__ void k_emit_level(TreeShape ts, int level, const unsigned int* __rest
         a.w = as_f((int)tl); b.w = as_f((int)tr);
         rec[0] = a; rec[1] = b;
         #pragma unroll
-        for (int v = 0; v < 3; ++v) { rec[2 + v] = tris[tl * 3 + v]; rec[5 + v] = tris[tr * 3 + v]; }
+        for (int v = 0; v < 3; ++v) {
+            float4 l = tris[tl * 3 + v], r = tris[tr * 3 + v];
+            if (v == 0) { l.w = as_f((int)tl); r.w = as_f((int)tr); }     // the ids again, inside the 96 bytes a leaf visit reads
+            rec[2 + v] = l; rec[5 + v] = r;
+        }
     }
 }
 

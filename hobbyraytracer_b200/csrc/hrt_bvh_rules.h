@@ -14,6 +14,8 @@
 //     (code, bottom-node index); hierarchy by the longest-common-prefix rule of Karras 2012 with the position as the
 //     tie-breaker; internal node i of the hierarchy is node i, the root is node 0.
 #pragma once
+#include <math.h>
+#include <stddef.h>
 #include <stdint.h>
 
 #if defined(__CUDACC__)
@@ -159,6 +161,120 @@ HRT_RULE_HD void rule_karras(const uint64_t* codes, int64_t n, int64_t i, int64_
     }
     split = i + s * d + (d < 0 ? -1 : 0);
     first = d > 0 ? i : j; last = d > 0 ? j : i;
+}
+
+} // namespace hrt
+
+// ---- (4) 8-wide collapse of a two-child tree (hrt_types.h, WNode) ------------------------------------------------------
+// Shared by the host builder (hrt_host.cpp, build_wide) and the device builder (hrt_bvh_gpu.cu, k_wide_level) so that both
+// produce the same bytes.  A wide node is made from one node of the two-child tree (`fast_nodes` format: both children's
+// boxes stored in the parent): starting from its two children, the inner child with the largest half area is replaced by
+// its own two children until there are eight or no inner child is left (ties: the earlier position).  The children are
+// then put into slots by a greedy assignment on the alignment of (child centre - node centre) with the slot's octant
+// direction, and their boxes are quantised outwards on the node's 8-bit grid.  Wide nodes are numbered breadth first: the
+// inner children of the nodes of one level, taken in node order and slot order, are the nodes of the next level.
+namespace hrt {
+
+struct WideItem { int child[8]; float lo[8][3], hi[8][3]; int count; };
+
+HRT_RULE_HD float rule_half_area(const float* lo, const float* hi)
+{
+    const float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+    const float a = dx * dy, b = dy * dz, c = dz * dx;
+    return (a + b) + c;
+}
+HRT_RULE_HD int rule_f2i(float f) { union { float f; int i; } u; u.f = f; return u.i; }
+template <class F4>
+HRT_RULE_HD void rule_node_children(const F4* nodes, int n, int& c0, int& c1, float* lo0, float* hi0, float* lo1, float* hi1)
+{
+    const F4 n0 = nodes[4 * (size_t)n], n1 = nodes[4 * (size_t)n + 1], n2 = nodes[4 * (size_t)n + 2], n3 = nodes[4 * (size_t)n + 3];
+    lo0[0] = n0.x; hi0[0] = n0.y; lo0[1] = n0.z; hi0[1] = n0.w; lo0[2] = n2.x; hi0[2] = n2.y;
+    lo1[0] = n1.x; hi1[0] = n1.y; lo1[1] = n1.z; hi1[1] = n1.w; lo1[2] = n2.z; hi1[2] = n2.w;
+    c0 = rule_f2i(n3.x); c1 = rule_f2i(n3.y);
+}
+template <class F4>
+HRT_RULE_HD void rule_wide_gather(const F4* nodes, int n, WideItem& w)
+{
+    rule_node_children(nodes, n, w.child[0], w.child[1], w.lo[0], w.hi[0], w.lo[1], w.hi[1]);
+    w.count = 2;
+    while (w.count < 8) {
+        int best = -1; float best_area = -1.0f;
+        for (int i = 0; i < w.count; ++i) {
+            if (w.child[i] < 0) continue;
+            const float a = rule_half_area(w.lo[i], w.hi[i]);
+            if (best < 0 || a > best_area) { best = i; best_area = a; }
+        }
+        if (best < 0) break;
+        const int m = w.child[best];
+        rule_node_children(nodes, m, w.child[best], w.child[w.count], w.lo[best], w.hi[best], w.lo[w.count], w.hi[w.count]);
+        ++w.count;
+    }
+}
+
+constexpr int WIDE_EXP_MIN = 27, WIDE_EXP_MAX = 239;      // biased exponents of the grid step: 2^-100 .. 2^112
+
+// Fills p, meta and q of `out` and leaves the slot of every gathered child in slot_of[]; out.child[] is left to the caller
+// (it depends on the numbering).  Returns false when the node box cannot be represented (non-finite or > 2^119 wide).
+template <class WN>
+HRT_RULE_HD bool rule_wide_pack(const WideItem& w, WN& out, int* slot_of)
+{
+    float lo[3], hi[3];
+    for (int a = 0; a < 3; ++a) {
+        lo[a] = w.lo[0][a]; hi[a] = w.hi[0][a];
+        for (int i = 1; i < w.count; ++i) { if (w.lo[i][a] < lo[a]) lo[a] = w.lo[i][a]; if (w.hi[i][a] > hi[a]) hi[a] = w.hi[i][a]; }
+    }
+    bool ok = true;
+    int eb[3]; double step[3];
+    for (int a = 0; a < 3; ++a) {
+        const double ext = (double)hi[a] - (double)lo[a];
+        if (!(ext >= 0.0) || !(ext < 1.0e36) || !(lo[a] > -1.0e36f) || !(lo[a] < 1.0e36f)) { ok = false; eb[a] = WIDE_EXP_MAX; step[a] = 1.0; continue; }
+        int k = WIDE_EXP_MIN - 127;
+        if (ext > 0.0) { int e2; (void)frexp(ext / 255.0, &e2); k = e2; }     // 2^k >= ext / 255
+        if (k < WIDE_EXP_MIN - 127) k = WIDE_EXP_MIN - 127;
+        if (k > WIDE_EXP_MAX - 127) { ok = false; k = WIDE_EXP_MAX - 127; }
+        eb[a] = k + 127; step[a] = ldexp(1.0, k);
+        out.p[a] = lo[a];
+    }
+    // slots: greedy on the alignment of the child's centre offset with the slot's octant direction
+    float off[8][3];
+    for (int i = 0; i < w.count; ++i)
+        for (int a = 0; a < 3; ++a) {
+            const float cn = 0.5f * lo[a] + 0.5f * hi[a], cc = 0.5f * w.lo[i][a] + 0.5f * w.hi[i][a];
+            off[i][a] = cc - cn;
+        }
+    unsigned used_slots = 0, placed = 0;
+    for (int round = 0; round < w.count; ++round) {
+        int bi = -1, bs = -1; float bc = 0.0f;
+        for (int i = 0; i < w.count; ++i) {
+            if (placed & (1u << i)) continue;
+            for (int s = 0; s < 8; ++s) {
+                if (used_slots & (1u << s)) continue;
+                const float x = (s & 1) ? off[i][0] : -off[i][0], y = (s & 2) ? off[i][1] : -off[i][1], z = (s & 4) ? off[i][2] : -off[i][2];
+                const float c = (x + y) + z;
+                if (bi < 0 || c > bc) { bi = i; bs = s; bc = c; }
+            }
+        }
+        slot_of[bi] = bs; placed |= 1u << bi; used_slots |= 1u << bs;
+    }
+    out.meta = (uint32_t)eb[0] | ((uint32_t)eb[1] << 8) | ((uint32_t)eb[2] << 16) | (used_slots << 24);
+    for (int a = 0; a < 3; ++a) for (int s = 0; s < 8; ++s) { out.q[2 * a][s] = 255; out.q[2 * a + 1][s] = 0; }     // empty slots: inverted box
+    for (int i = 0; i < w.count; ++i) {
+        const int s = slot_of[i];
+        for (int a = 0; a < 3; ++a) {
+            const double p = (double)lo[a];
+            double fl = floor(((double)w.lo[i][a] - p) / step[a]), fh = ceil(((double)w.hi[i][a] - p) / step[a]);
+            if (!(fl >= 0.0)) fl = 0.0;
+            if (fl > 255.0) fl = 255.0;
+            if (!(fh >= 0.0)) fh = 0.0;
+            if (fh > 255.0) fh = 255.0;
+            int ql = (int)fl, qh = (int)fh;
+            while (ql > 0 && p + (double)ql * step[a] > (double)w.lo[i][a]) --ql;
+            while (qh < 255 && p + (double)qh * step[a] < (double)w.hi[i][a]) ++qh;
+            if (p + (double)qh * step[a] < (double)w.hi[i][a]) ok = false;
+            out.q[2 * a][s] = (uint8_t)ql; out.q[2 * a + 1][s] = (uint8_t)qh;
+        }
+    }
+    return ok;
 }
 
 } // namespace hrt

@@ -10,6 +10,7 @@
 #include "hrt_bvh_rules.h"
 
 #include <algorithm>
+#include <array>
 #include <chrono>
 #include <cmath>
 #include <atomic>
@@ -418,6 +419,59 @@ void build_lbvh_host(const std::vector<float>& bmin, const std::vector<float>& b
 }
 
 // ------------------------------------------------------------------------------------------------------------
+// 8-wide collapse (hrt_bvh_rules.h (4)), breadth first: the inner children of the nodes of one level, in node order and
+// slot order, are the nodes of the next level - the numbering the device builder reproduces with one scan per level.
+// ------------------------------------------------------------------------------------------------------------
+void build_wide(const FastBvh& fast, WideBvh& out)
+{
+    out.nodes.clear(); out.root = fast.root; out.depth = 0; out.ok = true;
+    if (fast.root < 0) return;                                           // empty, or a single item: the root is that leaf
+    std::vector<int> level{fast.root}, next;                             // two-child nodes that become the wide nodes of this level
+    size_t base = 0;                                                     // wide index of level[0]
+    std::atomic<bool> ok{true};
+    while (!level.empty()) {
+        ++out.depth;
+        const size_t n = level.size();
+        out.nodes.resize(base + n);
+        std::vector<uint8_t> inner_count(n);
+        std::vector<std::array<int, 8>> inner(n);
+        parallel_chunks(n, 4096, [&](size_t, size_t lo, size_t hi) {
+            for (size_t i = lo; i < hi; ++i) {
+                WideItem w; rule_wide_gather(fast.nodes.data(), level[i], w);
+                WNode& node = out.nodes[base + i];
+                int slot_of[8];
+                if (!rule_wide_pack(w, node, slot_of)) ok = false;
+                int by_slot[8]; for (int s = 0; s < 8; ++s) by_slot[s] = 0x7fffffff;       // 0x7fffffff: empty
+                for (int c = 0; c < w.count; ++c) by_slot[slot_of[c]] = w.child[c];
+                int k = 0;
+                for (int s = 0; s < 8; ++s) {
+                    node.child[s] = by_slot[s] == 0x7fffffff ? -1 : by_slot[s];          // inner children are renumbered below
+                    if (by_slot[s] != 0x7fffffff && by_slot[s] >= 0) inner[i][(size_t)k++] = s;
+                }
+                inner_count[i] = (uint8_t)k;
+            }
+        });
+        const size_t next_base = base + n;
+        size_t total = 0;
+        std::vector<size_t> first(n);
+        for (size_t i = 0; i < n; ++i) { first[i] = total; total += inner_count[i]; }
+        next.resize(total);
+        parallel_chunks(n, 4096, [&](size_t, size_t lo, size_t hi) {
+            for (size_t i = lo; i < hi; ++i) {
+                WNode& node = out.nodes[base + i];
+                for (int k = 0; k < inner_count[i]; ++k) {
+                    const int s = inner[i][(size_t)k];
+                    next[first[i] + (size_t)k] = node.child[s];
+                    node.child[s] = (int)(next_base + first[i] + (size_t)k);
+                }
+            }
+        });
+        base = next_base; level.swap(next);
+    }
+    out.root = 0; out.ok = ok;
+}
+
+// ------------------------------------------------------------------------------------------------------------
 // Exact repack of a decoded Radiance image (texture.cpp:99-115 -> stb_image stbi__hdr_convert: byte * 2^(e-136))
 // into one 32-bit word per texel; refuses (returns false) unless every texel round-trips bit for bit.
 // ------------------------------------------------------------------------------------------------------------
@@ -587,7 +641,7 @@ void build_mesh_host(HostShape& sh, int bvh_mode, uint64_t seed, int shape_id, i
         a3.x = T[3]; a3.y = T[4]; a3.z = T[5]; a3.w = 0;
         sh.attrs4[i * 4] = a0; sh.attrs4[i * 4 + 1] = a1; sh.attrs4[i * 4 + 2] = a2; sh.attrs4[i * 4 + 3] = a3;
     }
-    sh.leaves.clear(); sh.fast = FastBvh(); sh.last_tri_r = -1;
+    sh.leaves.clear(); sh.fast = FastBvh(); sh.wide = WideBvh(); sh.last_tri_r = -1;
     if (fast && sh.ref.root >= 0) {
         t0 = now_ms();
         size_t n_nodes = sh.ref.nodes.size() / 2;
@@ -603,6 +657,7 @@ void build_mesh_host(HostShape& sh, int bvh_mode, uint64_t seed, int shape_id, i
             rec[0] = a; rec[1] = b;
             int il = (int)tl, ir = (int)tr; std::memcpy(&rec[0].w, &il, 4); std::memcpy(&rec[1].w, &ir, 4);
             for (int v = 0; v < 3; ++v) { rec[2 + v] = sh.tris4[tl * 3 + v]; rec[5 + v] = sh.tris4[tr * 3 + v]; }
+            std::memcpy(&rec[2].w, &il, 4); std::memcpy(&rec[5].w, &ir, 4);   // the ids again, inside the 96 bytes a leaf visit reads
             sh.leaves.insert(sh.leaves.end(), rec, rec + 8);
             sh.last_tri_r = ir;
         }
@@ -610,6 +665,7 @@ void build_mesh_host(HostShape& sh, int bvh_mode, uint64_t seed, int shape_id, i
             build_lbvh_host(bmin, bmax, sh.fast);
             if (sh.fast.depth > FAST_MAX_DEPTH) build_fast_bvh(bmin, bmax, sh.fast, nt);   // same decision as the device builder's fallback
         } else build_fast_bvh(bmin, bmax, sh.fast, nt);
+        build_wide(sh.fast, sh.wide);
         ms_fast += now_ms() - t0;
     }
     if (getenv("HRT_DEBUG_BUILD")) fprintf(stderr, "[hrt] host build of shape %d: %lld triangles, total %.2f ms (reference topology so far %.2f, fast tree so far %.2f)\n",
@@ -678,11 +734,12 @@ std::string flatten(HostScene& s, int bvh_mode, uint64_t seed)
         }
     }
     s.tlas_cull_scale = any_quat ? cull_scale : 0.0f;
-    s.tlas = FastBvh(); s.has_bounds = false;
+    s.tlas = FastBvh(); s.tlas_wide = WideBvh(); s.has_bounds = false;
     if (fast && !s.objects.empty()) {
         // float(double) may round inwards by half an ulp: push the bounds one step outwards
         for (size_t k = 0; k < obmin.size(); ++k) { obmin[k] = std::nextafter(obmin[k], -std::numeric_limits<float>::infinity()); obmax[k] = std::nextafter(obmax[k], std::numeric_limits<float>::infinity()); }
         build_fast_bvh(obmin, obmax, s.tlas, 1);
+        build_wide(s.tlas, s.tlas_wide);
         s.has_bounds = true;
         for (int a = 0; a < 3; ++a) { s.bounds_lo[a] = 3.0e38f; s.bounds_hi[a] = -3.0e38f; }
         for (size_t k = 0; k < obmin.size(); ++k) {

@@ -42,6 +42,13 @@ struct FastBvh {
     int depth = 0;
 };
 
+struct WideBvh {                     // 8-wide collapse of a FastBvh (hrt_bvh_rules.h (4)); breadth-first numbering, root = node 0
+    std::vector<WNode> nodes;
+    int root = -1;                   // >= 0 node, < 0 leaf ~item (a tree over one item), -1 with no nodes: empty
+    int depth = 0;
+    bool ok = true;                  // false: some node box is not representable on the 8-bit grid (unbounded entries)
+};
+
 struct HostShape {
     int kind = SHAPE_SPHERE;
     float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -67,6 +74,7 @@ struct HostShape {
     int mesh_index = -1;
     RefBvh ref;
     FastBvh fast;
+    WideBvh wide;
     std::vector<float4> tris4, attrs4;   // device layouts of hrt_types.h (DMesh::tris, DMesh::attrs)
     std::vector<float4> leaves;          // DMesh::fast_leaves
     // HRT_BVH_LBVH_GPU: flatten() leaves the mesh to the device builder (gpu_pending); hrt_scene_commit then stores the
@@ -101,6 +109,7 @@ struct HostScene {
     std::vector<DXform> d_xforms;
     std::vector<int> mesh_shapes;    // DScene::meshes[i] is built from shapes[mesh_shapes[i]]
     FastBvh tlas;
+    WideBvh tlas_wide;
     float tlas_cull_scale = 1.0f;
     float bounds_lo[3] = {0, 0, 0}, bounds_hi[3] = {0, 0, 0};   // union of the world-list entries' padded bounds
     bool has_bounds = false;         // false: some entry is unbounded (or reference-order scene)
@@ -121,6 +130,8 @@ void build_lbvh_host(const std::vector<float>& bmin, const std::vector<float>& b
 void build_mesh_host(HostShape& sh, int bvh_mode, uint64_t seed, int shape_id, int n_threads, double& ms_ref, double& ms_fast);
 // Binned-SAH BVH2 over arbitrary boxes (used for meshes and for the top-level BVH).
 void build_fast_bvh(const std::vector<float>& bmin, const std::vector<float>& bmax, FastBvh& out, int n_threads);
+// 8-wide collapse of `fast` (hrt_bvh_rules.h (4)): the tree the hot kernels walk.
+void build_wide(const FastBvh& fast, WideBvh& out);
 void triangle_boxes(const HostShape& sh, std::vector<float>& bmin, std::vector<float>& bmax);   // triangle.cpp:133-151
 
 // Fills d_objects / d_xforms / tlas; builds the per-mesh BVHs.  Returns "" or an error message.

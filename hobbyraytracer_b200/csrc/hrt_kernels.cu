@@ -17,6 +17,7 @@
 
 #include "hrt_kernels.h"
 #include "hrt_shade.cuh"
+#include "hrt_wide.cuh"
 
 namespace hrt {
 
@@ -32,51 +33,76 @@ __device__ __forceinline__ RngKey make_key(uint64_t seed, uint32_t index, uint32
 
 // ---- K7 ---------------------------------------------------------------------------------------------------------------
 #ifndef HRT_BATCH_MIN_BLOCKS
-#define HRT_BATCH_MIN_BLOCKS 8      // 16 M incoherent rays vs 10.5 M triangles on B200: 523 (4 blocks) / 591 (6) / 709 (8) Mrays/s
+#define HRT_BATCH_MIN_BLOCKS 4
 #endif
-#ifndef HRT_REFILL_THRESH
-#define HRT_REFILL_THRESH 24        // a warp goes back for new rays as soon as fewer than this many lanes are still walking
-#endif
-// Persistent warps with per-lane refill: a lane whose walk is over takes the next ray from a global counter while the
-// other lanes keep the state of theirs (Walk), so the warp's node loop stays full whatever the spread of walk lengths.
-__global__ void __launch_bounds__(BLOCK, HRT_BATCH_MIN_BLOCKS) k_trace_batch(DScene s, const float4* __restrict__ rays, long long n, Hit* __restrict__ hits, uint64_t seed,
-                                                                            unsigned long long* __restrict__ counter)
+// Pending rays (pass 1 could not decide: hrt_wide.cuh) are listed here and settled by k_resolve_* afterwards.
+struct PendList { unsigned int* idx; unsigned int* count; };
+__device__ __forceinline__ void pend_push(const PendList& p, unsigned int i) { p.idx[atomicAdd(p.count, 1u)] = i; }
+
+// Persistent warps over the 8-wide trees: a lane whose walk is over takes the next ray from a global counter while the other
+// lanes keep theirs, and the warp advances in phases (hrt_wide.cuh).  Scenes without wide trees: one ray per thread (_plain).
+__global__ void __launch_bounds__(BLOCK) k_trace_batch_plain(DScene s, const float4* __restrict__ rays, long long n, Hit* __restrict__ hits, uint64_t seed)
 {
-    if (!s.fast) {                                                                // reference visiting order: one ray per thread
-        const long long stride = (long long)gridDim.x * blockDim.x;
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-            float4 a = __ldg(rays + 2 * i), b = __ldg(rays + 2 * i + 1);
-            Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
-            hits[i] = trace_ref(s, r, a.w, b.w, make_key(seed, (uint32_t)i, (uint32_t)(i >> 32), 0), 0);
-        }
-        return;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        float4 a = __ldg(rays + 2 * i), b = __ldg(rays + 2 * i + 1);
+        Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
+        const RngKey key = make_key(seed, (uint32_t)i, (uint32_t)(i >> 32), 0);
+        hits[i] = s.fast ? trace_fast<false>(s, r, a.w, b.w, key, 0, nullptr) : trace_ref(s, r, a.w, b.w, key, 0);
     }
+}
+__global__ void __launch_bounds__(BLOCK, HRT_BATCH_MIN_BLOCKS) k_trace_batch(DScene s, const float4* __restrict__ rays, long long n, Hit* __restrict__ hits, uint64_t seed,
+                                                                            unsigned long long* __restrict__ counter, PendList pend)
+{
+    __shared__ int stack_mem[WIDE_STACK * BLOCK];
+    WideSmemStack<BLOCK> st; st.base = stack_mem + threadIdx.x; st.sp = 0;
     const unsigned int lane = threadIdx.x & 31u;
-    Walk w; w.live = false; w.pre = 1;
+    WideLane L; L.live = false;
     long long idx = -1; bool exhausted = false;
-    Collector* none = nullptr;
     for (;;) {
-        const bool need = idx < 0;
-        const unsigned int m = __ballot_sync(0xffffffffu, need);
-        if (m && !exhausted) {
-            unsigned long long base = 0;
-            if (lane == (unsigned int)(__ffs(m) - 1)) base = atomicAdd(counter, (unsigned long long)__popc(m));
-            base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-            if (need) {
+        const int walking = __popc(__ballot_sync(0xffffffffu, L.live));
+        if (walking < (exhausted ? 1 : HRT_WIDE_REFILL)) {
+            if (idx >= 0 && !L.live) {                                            // a finished walk: its record, or its place on the pending list
+                const Hit h = wide_result(L);
+                hits[idx] = h;
+                if (h.flags & HIT_PENDING) pend_push(pend, (unsigned int)idx);
+                idx = -1;
+            }
+            if (!exhausted) {
+                const unsigned int m = __ballot_sync(0xffffffffu, idx < 0);
+                unsigned long long base = 0;
+                if (lane == (unsigned int)(__ffs(m) - 1)) base = atomicAdd(counter, (unsigned long long)__popc(m));
+                base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
                 const long long my = (long long)base + __popc(m & ((1u << lane) - 1u));
-                if (my < n) {
-                    idx = my;
+                if (idx < 0 && my < n) {
                     float4 a = __ldg(rays + 2 * my), b = __ldg(rays + 2 * my + 1);
                     Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
-                    trace_begin(w, s, r, a.w, b.w);
+                    Hit early;
+                    st.sp = 0;
+                    if (wide_begin(L, s, r, a.w, b.w, early)) idx = my;
+                    else {                                                        // nothing to walk: answered on the spot, or trace_ref's business
+                        if (L.b.bad) { early = wide_result(L); pend_push(pend, (unsigned int)my); }
+                        hits[my] = early;
+                    }
                 }
+                if ((long long)base + __popc(m) >= n) exhausted = true;
             }
-            if ((long long)base + __popc(m) >= n) exhausted = true;
         }
-        if (!__any_sync(0xffffffffu, idx >= 0)) break;
         const RngKey key = make_key(seed, (uint32_t)idx, (uint32_t)((unsigned long long)idx >> 32), 0);
-        walk_run<false, false, true>(w, s, *none, key, 0, nullptr, exhausted ? 1 : HRT_REFILL_THRESH);
-        if (idx >= 0 && !w.live) { hits[idx] = trace_finish<false>(w, s, key, 0, nullptr); idx = -1; }
+        if (!wide_round(L, s, st, key, 0) && exhausted) {
+            if (!__any_sync(0xffffffffu, idx >= 0)) break;
+        }
+    }
+}
+// pass 2 of the rays k_trace_batch left pending
+__global__ void __launch_bounds__(BLOCK) k_resolve_batch(DScene s, const float4* __restrict__ rays, Hit* __restrict__ hits, uint64_t seed, PendList pend)
+{
+    const unsigned int n = *pend.count;
+    for (unsigned int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const unsigned int i = pend.idx[k];
+        float4 a = __ldg(rays + 2 * (size_t)i), b = __ldg(rays + 2 * (size_t)i + 1);
+        Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
+        hits[i] = wide_resolve(s, r, a.w, b.w, make_key(seed, i, 0u, 0), 0, hits[i]);
     }
 }
 __global__ void __launch_bounds__(BLOCK) k_split_hits(const Hit* __restrict__ hits, long long n, uint32_t* __restrict__ prim, float* __restrict__ t)
@@ -365,6 +391,9 @@ __device__ __forceinline__ void acc_flush(FilmAcc& a, long long* film, int pix)
 // beats spilling there).  The host picks per chunk from the secondary-rays-per-camera-path ratio it reads in the control block.
 // Secondary rays of queue q with per-lane refill (scenes with meshes: the walks are long and their lengths spread widely).
 // Runs before k_wave2_trace, which is then told to skip its own lock-step pass over these entries.
+#ifndef HRT_REFILL_THRESH
+#define HRT_REFILL_THRESH 24
+#endif
 #ifndef HRT_DYN_MIN_BLOCKS
 #define HRT_DYN_MIN_BLOCKS 8
 #endif
@@ -602,10 +631,15 @@ int grid_for(long long n, int sm_count, int per_sm)
 } // namespace
 
 // ---- launchers -------------------------------------------------------------------------------------------------------------
-void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed, unsigned long long* d_counter, int sm_count, cudaStream_t st, uint64_t* launches)
+void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed, unsigned long long* d_counter,
+                        unsigned int* d_pend_idx, unsigned int* d_pend_count, int sm_count, cudaStream_t st, uint64_t* launches)
 {
     cudaMemsetAsync(d_counter, 0, sizeof(unsigned long long), st);
-    k_trace_batch<<<grid_for(n, sm_count, s.fast ? HRT_BATCH_MIN_BLOCKS : 16), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed, d_counter); *launches += 1;
+    cudaMemsetAsync(d_pend_count, 0, sizeof(unsigned int), st);
+    PendList pend; pend.idx = d_pend_idx; pend.count = d_pend_count;
+    if (!s.wide) { k_trace_batch_plain<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed); *launches += 1; return; }
+    k_trace_batch<<<grid_for(n, sm_count, HRT_BATCH_MIN_BLOCKS), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed, d_counter, pend);
+    k_resolve_batch<<<sm_count * 2, BLOCK, 0, st>>>(s, d_rays, d_hits, seed, pend); *launches += 2;
 }
 void launch_split_hits(const Hit* d_hits, long long n, uint32_t* d_prim, float* d_t, int sm_count, cudaStream_t st, uint64_t* launches)
 {

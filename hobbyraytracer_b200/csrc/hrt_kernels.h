@@ -48,7 +48,9 @@ struct WaveJob {
     long long* film;                    // npix * FILM_LANES
 };
 
-void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed, unsigned long long* d_counter, int sm_count, cudaStream_t st, uint64_t* launches);
+// d_pend_idx (n entries) / d_pend_count (one word): scratch for the rays that need pass 2 (hrt_wide.cuh)
+void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed, unsigned long long* d_counter,
+                        unsigned int* d_pend_idx, unsigned int* d_pend_count, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_split_hits(const Hit* d_hits, long long n, uint32_t* d_prim, float* d_t, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_eval_batch(const DScene& s, const float4* d_rays, const Hit* d_hits, long long n, float* d_normal, float* d_uv, uint8_t* d_front,
                        int sm_count, cudaStream_t st, uint64_t* launches);

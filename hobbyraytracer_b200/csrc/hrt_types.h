@@ -44,18 +44,34 @@ struct DObject {
 //  tris       : 3 x float4 per triangle in input order: (p0, -) (p1, -) (p2, -)
 //  attrs      : 4 x float4 per triangle in input order: (n0, uv0.x) (n1, uv0.y) (n2, uv1.x) (uv1.y, uv2.x, uv2.y, -)
 //  fast_leaves: one 128-byte record per BOTTOM node of the reference topology (a node whose children are triangles),
-//               8 x float4: (min.xyz, triL) (max.xyz, triR) (L.p0) (L.p1) (L.p2) (R.p0) (R.p1) (R.p2).  The box is
+//               8 x float4: (min.xyz, triL) (max.xyz, triR) (L.p0, triL) (L.p1) (L.p2) (R.p0, triR) (R.p1) (R.p2): the last
+//               96 bytes are all a leaf visit reads (three 256-bit loads); the box only when a triangle accepts.  The box is
 //               the reference node's box, tested with the reference's own slab arithmetic, so which triangles a
 //               ray gets to test below t_min (ITriangle::hit ignores t_min, triangle.cpp:57-131) is unchanged.
 //  fast_nodes : binned-SAH BVH2 over those bottom nodes — 4 x float4 per node: (c0.lo.x c0.hi.x c0.lo.y c0.hi.y)
 //               (c1.lo.x c1.hi.x c1.lo.y c1.hi.y) (c0.lo.z c0.hi.z c1.lo.z c1.hi.z) (child0, child1, -, -);
 //               child >= 0 is a node, child < 0 is leaf record ~child.
+// Wide node (hrt_wide.cuh): 8 children with boxes quantised to 8 bits on a per-node grid, 96 bytes = three 32-byte
+// sectors read with three 256-bit loads.
+//   [ 0] p[3]    grid origin (the node box's min corner)
+//   [12] meta    ex | ey << 8 | ez << 16 | valid << 24: biased exponents of the grid steps (step = 2^(e - 127)) and the
+//                mask of occupied child slots
+//   [16] q[6][8] lo.x hi.x lo.y hi.y lo.z hi.z of the eight slots: child box = [p + lo * step, p + hi * step], a superset
+//                of the child's true box
+//   [64] child[8] >= 0: wide node, < 0: leaf ~id (mesh: leaf record, top level: world-list entry)
+// Slot s holds the child whose centre lies most towards ((s & 1) ? +x : -x, (s & 2) ? +y : -y, (s & 4) ? +z : -z) of the
+// node centre, so that slot ^ (sign bits of the ray direction) orders the children roughly front to back (Ylitie et al. 2017).
+struct WNode { float p[3]; uint32_t meta; uint8_t q[6][8]; int32_t child[8]; };
+static_assert(sizeof(WNode) == 96, "WNode layout");
+
 struct DMesh {
     const float4* ref_nodes;
     const float4* tris;
     const float4* attrs;
     const float4* fast_nodes;
     const float4* fast_leaves;
+    const WNode* wide_nodes; // 8-wide collapse of fast_nodes (the tree the hot kernels walk)
+    int wide_root;          // >= 0 node, < 0 leaf ~id
     int ref_root;           // -1: empty mesh
     int fast_root;          // >= 0 node, < 0 leaf ~id; only valid when ref_root >= 0
     int64_t n_tri;
@@ -79,6 +95,9 @@ struct DScene {
     const DTexture* textures;
     const float4* tlas_nodes;   // top-level BVH over world-list entries (same node format as fast_nodes), or null
     int tlas_root;              // >= 0 node, < 0 leaf = object ~id
+    const WNode* tlas_wide;     // 8-wide collapse of tlas_nodes
+    int tlas_wide_root;
+    int wide;                   // 1: the wide trees exist for every level (fast scenes whose boxes fit the 8-bit grids): hrt_wide.cuh walks them
     int n_objects;
     int n_materials;
     int n_textures;

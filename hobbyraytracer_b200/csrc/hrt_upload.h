@@ -24,6 +24,8 @@ DScene make_dscene(HostScene& s, Up& up)
         m.attrs = (const float4*)up.put(sh.attrs4.data(), sh.attrs4.size() * sizeof(float4));
         m.fast_nodes = (const float4*)up.put(sh.fast.nodes.data(), sh.fast.nodes.size() * sizeof(float4));
         m.fast_leaves = (const float4*)up.put(sh.leaves.data(), sh.leaves.size() * sizeof(float4));
+        m.wide_nodes = (const WNode*)up.put(sh.wide.nodes.data(), sh.wide.nodes.size() * sizeof(WNode));
+        m.wide_root = sh.wide.root;
         m.ref_root = sh.ref.root; m.fast_root = sh.fast.root;
         m.n_tri = sh.n_tri; m.prim_base = (uint32_t)sh.prim_base; m.material = sh.material;
         meshes[i] = m;
@@ -48,11 +50,16 @@ DScene make_dscene(HostScene& s, Up& up)
     d.textures = (const DTexture*)up.put_copy(tex.data(), tex.size() * sizeof(DTexture));
     d.tlas_nodes = (const float4*)up.put(s.tlas.nodes.data(), s.tlas.nodes.size() * sizeof(float4));
     d.tlas_root = s.tlas.root;
+    d.tlas_wide = (const WNode*)up.put(s.tlas_wide.nodes.data(), s.tlas_wide.nodes.size() * sizeof(WNode));
+    d.tlas_wide_root = s.tlas_wide.root;
     d.n_objects = (int)s.d_objects.size();
     d.n_materials = (int)s.materials.size();
     d.n_textures = (int)s.textures.size();
     d.background = s.background;
     d.fast = fast ? 1 : 0;
+    d.wide = (fast && s.tlas_wide.ok) ? 1 : 0;
+    for (const DMesh& m : meshes) if (m.ref_root >= 0 && m.wide_root >= 0 && m.wide_nodes == nullptr) d.wide = 0;
+    for (size_t i = 0; i < s.mesh_shapes.size(); ++i) if (!s.shapes[(size_t)s.mesh_shapes[i]].wide.ok) d.wide = 0;
     d.refill_secondary = (fast && !meshes.empty()) ? 1 : 0;
     d.tlas_cull_scale = s.tlas_cull_scale;
     d.has_bounds = (fast && s.has_bounds) ? 1 : 0;

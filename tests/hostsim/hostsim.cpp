@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "../../hobbyraytracer_b200/csrc/hrt_shade.cuh"
+#include "../../hobbyraytracer_b200/csrc/hrt_wide.cuh"
 #include "../../hobbyraytracer_b200/csrc/hrt_upload.h"
 
 using namespace hrt;
@@ -97,6 +98,25 @@ int hsim_trace_batch(hsim_scene* s, const float* rays, int64_t n, uint32_t* prim
         }
     });
     s->cnt.nodes = nodes; s->cnt.prims = prims; s->cnt.fallbacks = fb; s->cnt.amb = amb; s->cnt.bad = bad;
+    return 0;
+}
+// The same through the 8-wide trees (hrt_wide.cuh): pass 1 on the wide nodes, pending rays through trace_resolve.
+// out_steps (may be NULL) receives the number of node / leaf / entry steps; returns HRT_ERR_STATE when the scene has no wide trees.
+int hsim_trace_batch_wide(hsim_scene* s, const float* rays, int64_t n, uint32_t* prim_id, float* t, uint64_t rng_seed, uint64_t* out_steps)
+{
+    if (!s->host.committed) { g_err = "scene not committed"; return HRT_ERR_STATE; }
+    if (!s->d.wide) { g_err = "scene has no wide trees"; return HRT_ERR_STATE; }
+    std::atomic<unsigned long long> steps(0);
+    parallel_for(n, 4096, [&](int64_t i) {
+        const float* q = rays + i * 8;
+        Ray r; r.o = v3(q[0], q[1], q[2]); r.d = v3(q[4], q[5], q[6]);
+        RngKey key; key.k0 = (uint32_t)rng_seed; key.k1 = (uint32_t)(rng_seed >> 32); key.index = (uint32_t)i; key.sample = (uint32_t)(i >> 32); key.mode = 0;
+        unsigned long long st = 0;
+        Hit h = wide_trace_scalar(s->d, r, q[3], q[7], key, 0, &st);
+        steps += st;
+        prim_id[i] = h.prim; t[i] = h.prim != HRT_MISS ? h.t : 0.0f;
+    });
+    if (out_steps) *out_steps = steps;
     return 0;
 }
 // Texture::colourValue through the device header on the flattened scene (exercises the lossless RGBE repack of env maps)

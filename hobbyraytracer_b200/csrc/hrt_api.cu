@@ -129,7 +129,7 @@ Parked g_parked;
 void cuda_free_job(WaveJob& job)
 {
     for (int q = 0; q < 2; ++q) { cudaFree(job.rays[q]); cudaFree(job.thr[q]); cudaFree(job.res[q]); }
-    cudaFree(job.hits); cudaFree(job.ctl);
+    cudaFree(job.hits); cudaFree(job.pend); cudaFree(job.ctl);
     job = WaveJob{};
 }
 void trim_parked_locked()
@@ -144,7 +144,7 @@ void trim_parked_locked()
 void free_job(hrt_scene* s)
 {
     for (int q = 0; q < 2; ++q) { cudaFree(s->job.rays[q]); cudaFree(s->job.thr[q]); cudaFree(s->job.res[q]); }
-    cudaFree(s->job.hits); cudaFree(s->job.ctl);
+    cudaFree(s->job.hits); cudaFree(s->job.pend); cudaFree(s->job.ctl);
     s->job = WaveJob{}; s->job_capacity = 0;
 }
 void free_tb(hrt_scene* s)
@@ -180,6 +180,7 @@ int ensure_job(hrt_scene* s, unsigned int capacity)
         CK(cudaMalloc(&s->job.res[q], sizeof(float4) * (size_t)capacity));
     }
     CK(cudaMalloc(&s->job.hits, sizeof(Hit) * (size_t)capacity));
+    CK(cudaMalloc(&s->job.pend, sizeof(unsigned int) * (size_t)capacity));
     CK(cudaMalloc(&s->job.ctl, sizeof(WaveCtl)));
     if (!s->h_ctl) CK(cudaMallocHost(&s->h_ctl, sizeof(WaveCtl) * CTL_RING));
     s->job_capacity = capacity;
@@ -266,7 +267,8 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
     while (s->events.size() < (size_t)(EV_PER_CHUNK * CTL_RING + 2)) { cudaEvent_t e; CK(cudaEventCreate(&e)); s->events.push_back(e); }
     cudaEvent_t ev_begin = s->events[EV_PER_CHUNK * CTL_RING], ev_end = s->events[EV_PER_CHUNK * CTL_RING + 1];
 
-    WaveCtl init{}; init.total_paths = (mega || v1) ? total : wave2_total_claims(j);
+    const bool wide = s->d.wide && !mega && !v1 && !getenv("HRT_NO_WIDE");     // the pipeline over the 8-wide trees (hrt_wide.cuh)
+    WaveCtl init{}; init.total_paths = (mega || v1) ? total : (wide ? wave3_total_claims(j) : wave2_total_claims(j));
     CK(cudaMemcpyAsync(j.ctl, &init, sizeof(init), cudaMemcpyHostToDevice, st));
     CK(cudaEventRecord(ev_begin, st));
     s->stats.paths += total;
@@ -301,6 +303,7 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
             for (int k = 0; k < CHUNK; ++k, ++it) {
                 CK(cudaEventRecord(ev[2 * k], st));
                 if (v1) launch_wave_trace(s->d, j, it, s->sm_count, st, &s->stats.launches);
+                else if (wide) launch_wave3_trace(s->d, j, dc, it, s->sm_count, st, &s->stats.launches);
                 else launch_wave2_trace(s->d, j, dc, it, secondary_heavy, s->sm_count, st, &s->stats.launches);
                 CK(cudaEventRecord(ev[2 * k + 1], st));
                 if (v1) launch_wave_shade(s->d, j, dc, it, s->sm_count, st, &s->stats.launches);
@@ -445,7 +448,7 @@ int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed)
             continue;
         }
         sh.has_dev = true; sh.dev = b.mesh;
-        sh.n_ref_nodes = b.n_ref_nodes; sh.n_fast_nodes = b.n_fast_nodes; sh.n_leaves = b.n_leaves; sh.last_tri_r = b.last_tri_r;
+        sh.n_ref_nodes = b.n_ref_nodes; sh.n_fast_nodes = b.n_fast_nodes; sh.n_leaves = b.n_leaves; sh.n_wide_nodes = b.n_wide_nodes; sh.last_tri_r = b.last_tri_r;
         sh.fast.depth = b.depth;
         s->ms_build_gpu += b.ms_upload + b.ms_build; s->ms_build_upload += b.ms_upload; s->h2d_bytes += b.h2d_bytes;
         if (getenv("HRT_DEBUG_BUILD")) fprintf(stderr, "[hrt] device build of shape %d: %lld triangles, source %.1f MB (%s) uploaded in %.1f ms, built in %.1f ms\n",
@@ -467,11 +470,11 @@ int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed)
 int64_t hrt_scene_mesh_array(hrt_scene* s, int mesh_index, int which, void* out, int64_t capacity_bytes)
 {
     if (!s || !s->host.committed) { g_err = "scene not committed"; return HRT_ERR_STATE; }
-    if (mesh_index < 0 || (size_t)mesh_index >= s->meshes_view.size() || which < 0 || which > 4) { g_err = "bad argument"; return HRT_ERR_ARG; }
+    if (mesh_index < 0 || (size_t)mesh_index >= s->meshes_view.size() || which < 0 || which > 5) { g_err = "bad argument"; return HRT_ERR_ARG; }
     const HostShape& sh = s->host.shapes[(size_t)s->host.mesh_shapes[(size_t)mesh_index]];
     const DMesh& m = s->meshes_view[(size_t)mesh_index];
-    const void* src[5] = {m.ref_nodes, m.fast_nodes, m.fast_leaves, m.tris, m.attrs};
-    const size_t bytes[5] = {sh.n_ref_nodes * 32, sh.n_fast_nodes * 64, sh.n_leaves * 128, (size_t)sh.n_tri * 48, (size_t)sh.n_tri * 64};
+    const void* src[6] = {m.ref_nodes, m.fast_nodes, m.fast_leaves, m.tris, m.attrs, m.wide_nodes};
+    const size_t bytes[6] = {sh.n_ref_nodes * 32, sh.n_fast_nodes * 64, sh.n_leaves * 128, (size_t)sh.n_tri * 48, (size_t)sh.n_tri * 64, m.wide_nodes ? sh.n_wide_nodes * 96 : 0};
     if (out) {
         if (capacity_bytes < (int64_t)bytes[which]) { g_err = "buffer too small"; return HRT_ERR_ARG; }
         CK(cudaSetDevice(s->device));

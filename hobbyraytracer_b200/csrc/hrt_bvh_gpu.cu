@@ -8,11 +8,14 @@
 //                    records (DMesh::fast_leaves)
 //   k_centre_bounds, k_morton + one radix sort, k_karras, k_refit, k_depth:   Morton LBVH over the bottom nodes in the
 //                    fast_nodes format (both children's boxes in the node)
+//   k_wide_level, one exclusive scan, k_wide_link per level of the 8-wide collapse (DMesh::wide_nodes, the tree the hot
+//                    kernels walk): breadth first, numbering and bytes of hrt_host.cpp::build_wide (hrt_bvh_rules.h (4))
 // The arrays are bit-identical to the host mirror (HRT_BVH_LBVH_HOST): every rule is shared source (hrt_bvh_rules.h),
 // boxes are unions taken in a fixed operand order.  The two sorts are cub::DeviceRadixSort (stable LSD radix sort);
 // everything else is hand-written.  The tree shape is known from the triangle count alone, so the level loop runs
 // without any device -> host read; the only reads back are the validity flag, the depth and the last leaf's triangle.
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <cuda_runtime.h>
 
 #include <chrono>
@@ -254,6 +257,46 @@ __global__ void k_depth(long long n, const int* __restrict__ node_parent, const 
     if ((threadIdx.x & 31) == 0) atomicMax(depth, d);
 }
 
+// ---- 8-wide collapse, one level: item i (a node of the two-child tree) becomes wide node base + i ------------------------------
+// k_wide_level packs the node (boxes, slots) and leaves the two-child references of its inner children in child[] together with
+// their count; after an exclusive scan of the counts k_wide_link turns them into the indices of the next level and lists them.
+__global__ void k_wide_level(const float4* __restrict__ fast, const int* __restrict__ items, int n_items, int base, WNode* __restrict__ wide,
+                             int* __restrict__ inner_count, int* __restrict__ flags)
+{
+    const int i = blockIdx.x * TB + threadIdx.x;
+    if (i >= n_items) return;
+    WideItem w; rule_wide_gather(fast, items[i], w);
+    WNode node; int slot_of[8];
+    if (!rule_wide_pack(w, node, slot_of)) atomicOr(flags + 1, 1);
+    int by_slot[8];
+#pragma unroll
+    for (int s = 0; s < 8; ++s) by_slot[s] = 0x7fffffff;
+    for (int c = 0; c < w.count; ++c) {
+#pragma unroll
+        for (int s = 0; s < 8; ++s) if (slot_of[c] == s) by_slot[s] = w.child[c];
+    }
+    int k = 0;
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        node.child[s] = by_slot[s] == 0x7fffffff ? -1 : by_slot[s];
+        if (by_slot[s] != 0x7fffffff && by_slot[s] >= 0) ++k;
+    }
+    inner_count[i] = k;
+    wide[(size_t)base + (size_t)i] = node;
+}
+__global__ void k_wide_link(const int* __restrict__ first, int n_items, int base, int next_base, WNode* __restrict__ wide, int* __restrict__ next_items)
+{
+    const int i = blockIdx.x * TB + threadIdx.x;
+    if (i >= n_items) return;
+    WNode* node = wide + (size_t)base + (size_t)i;
+    const unsigned int valid = node->meta >> 24;
+    int k = first[i];
+    for (int s = 0; s < 8; ++s) {
+        const int ch = node->child[s];
+        if (((valid >> s) & 1u) && ch >= 0) { next_items[k] = ch; node->child[s] = next_base + k; ++k; }
+    }
+}
+
 struct Tmp {
     std::vector<void*> ptrs;
     ~Tmp() { for (void* p : ptrs) cudaFree(p); }
@@ -360,7 +403,34 @@ bool build_mesh_gpu(const MeshSource& src, int64_t n_tri, uint64_t seed, int sha
         GB_CK(cudaMemcpyAsync(&depth, d_depth, sizeof(int), cudaMemcpyDeviceToHost, st));
         fast_root = 0;
     }
-    int flags = 0;
+    // 8-wide collapse of the fast tree, breadth first (hrt_bvh_rules.h (4)); one small read back per level (the size of the next one)
+    WNode* d_wide = nullptr; size_t n_wide = 0; int wide_depth = 0;
+    if (n_leaves > 1) {
+        const size_t bound = n_leaves - 1;                                  // a wide node replaces at least one two-child node
+        WNode* d_wtmp; int *d_items[2], *d_cnt, *d_first;
+        if (!tmp.get(d_wtmp, bound) || !tmp.get(d_items[0], bound) || !tmp.get(d_items[1], bound) || !tmp.get(d_cnt, bound + 1) || !tmp.get(d_first, bound + 1)) { err = "out of device memory (wide collapse scratch)"; return false; }
+        size_t scan_bytes = 0;
+        GB_CK(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, d_cnt, d_first, (int)(bound + 1), st));
+        unsigned char* d_scan = nullptr; if (!tmp.get(d_scan, scan_bytes)) { err = "out of device memory (scan scratch)"; return false; }
+        GB_CK(cudaMemsetAsync(d_items[0], 0, sizeof(int), st));              // level 0: the root, two-child node 0
+        int n_items = 1, base = 0, cur_items = 0;
+        while (n_items > 0) {
+            k_wide_level<<<grid_for(n_items), TB, 0, st>>>(d_fast, d_items[cur_items], n_items, base, d_wtmp, d_cnt, d_flags); ++nl;
+            GB_CK(cub::DeviceScan::ExclusiveSum(d_scan, scan_bytes, d_cnt, d_first, n_items + 1, st));
+            k_wide_link<<<grid_for(n_items), TB, 0, st>>>(d_first, n_items, base, base + n_items, d_wtmp, d_items[cur_items ^ 1]); ++nl;
+            int total = 0;
+            GB_CK(cudaMemcpyAsync(&total, d_first + n_items, sizeof(int), cudaMemcpyDeviceToHost, st));
+            GB_CK(cudaStreamSynchronize(st));
+            base += n_items; n_items = total; cur_items ^= 1; ++wide_depth;
+        }
+        n_wide = (size_t)base;
+        float4* d_w4 = nullptr;
+        if (!keep(d_w4, n_wide * 6)) { err = "out of device memory (wide nodes)"; return false; }
+        d_wide = (WNode*)d_w4;
+        GB_CK(cudaMemcpyAsync(d_wide, d_wtmp, n_wide * sizeof(WNode), cudaMemcpyDeviceToDevice, st));
+    }
+    int flags = 0, wide_bad = 0;
+    GB_CK(cudaMemcpyAsync(&wide_bad, d_flags + 1, sizeof(int), cudaMemcpyDeviceToHost, st));
     GB_CK(cudaMemcpyAsync(&flags, d_flags, sizeof(int), cudaMemcpyDeviceToHost, st));
     GB_CK(cudaMemcpyAsync(&last_tri_r, reinterpret_cast<const int*>(d_leaves + 8 * (n_leaves - 1) + 1) + 3, sizeof(int), cudaMemcpyDeviceToHost, st));
     GB_CK(cudaStreamSynchronize(st));
@@ -372,7 +442,9 @@ bool build_mesh_gpu(const MeshSource& src, int64_t n_tri, uint64_t seed, int sha
 
     DMesh& m = out.mesh;
     m.ref_nodes = d_ref; m.tris = d_tris; m.attrs = d_attrs; m.fast_nodes = d_fast; m.fast_leaves = d_leaves;
+    m.wide_nodes = wide_bad ? nullptr : d_wide; m.wide_root = fast_root;      // wide_bad: boxes off the 8-bit grids - the scene keeps to the two-child walk
     m.ref_root = 0; m.fast_root = fast_root; m.n_tri = n_tri;
+    out.n_wide_nodes = n_wide; out.wide_depth = wide_depth;
     out.n_ref_nodes = n_nodes; out.n_fast_nodes = n_leaves > 1 ? n_leaves - 1 : 0; out.n_leaves = n_leaves;
     out.last_tri_r = last_tri_r; out.depth = depth;
     return true;

@@ -12,7 +12,8 @@ namespace hrt {
 
 struct GpuMeshBuild {
     DMesh mesh{};                    // device pointers + roots (prim_base / material are filled in by the caller)
-    size_t n_ref_nodes = 0, n_fast_nodes = 0, n_leaves = 0;
+    size_t n_ref_nodes = 0, n_fast_nodes = 0, n_leaves = 0, n_wide_nodes = 0;
+    int wide_depth = 0;
     int last_tri_r = -1;             // right triangle of the last bottom node (what a NaN-origin ray reports, hrt_upload.h)
     int depth = 0;                   // depth of the fast tree
     bool fallback = false;           // true: this mesh cannot be built here (why), the host builder takes over

@@ -670,7 +670,7 @@ void build_mesh_host(HostShape& sh, int bvh_mode, uint64_t seed, int shape_id, i
     }
     if (getenv("HRT_DEBUG_BUILD")) fprintf(stderr, "[hrt] host build of shape %d: %lld triangles, total %.2f ms (reference topology so far %.2f, fast tree so far %.2f)\n",
                                            shape_id, (long long)sh.n_tri, now_ms() - t_enter, ms_ref, ms_fast);
-    sh.n_ref_nodes = sh.ref.nodes.size() / 2; sh.n_fast_nodes = sh.fast.nodes.size() / 4; sh.n_leaves = sh.leaves.size() / 8;
+    sh.n_ref_nodes = sh.ref.nodes.size() / 2; sh.n_fast_nodes = sh.fast.nodes.size() / 4; sh.n_leaves = sh.leaves.size() / 8; sh.n_wide_nodes = sh.wide.nodes.size();
 }
 
 std::string flatten(HostScene& s, int bvh_mode, uint64_t seed)

@@ -81,7 +81,7 @@ struct HostShape {
     // device-built view here (has_dev) and make_dscene hands it out instead of uploading host arrays
     bool gpu_pending = false, has_dev = false;
     DMesh dev{};
-    size_t n_ref_nodes = 0, n_fast_nodes = 0, n_leaves = 0;   // element counts behind the DMesh pointers (either builder)
+    size_t n_ref_nodes = 0, n_fast_nodes = 0, n_leaves = 0, n_wide_nodes = 0;   // element counts behind the DMesh pointers (either builder)
     int last_tri_r = -1;                 // right triangle of the last bottom node, -1: empty mesh
 };
 

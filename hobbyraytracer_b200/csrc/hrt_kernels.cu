@@ -551,7 +551,7 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave2_shade(DScene s, WaveJob j
     WaveCtl* c = j.ctl;
     const int o = q ^ 1;
     const unsigned int n = c->n_front[q] + c->n_prim[q];
-    if (blockIdx.x == 0 && threadIdx.x == 0) { c->n_prim[o] = 0; c->sec_next[o] = 0; }   // the next trace pass works on queue o; nobody reads these here
+    if (blockIdx.x == 0 && threadIdx.x == 0) { c->n_prim[o] = 0; c->sec_next[o] = 0; c->pend_count = 0; }   // the next trace pass works on queue o; nobody reads these here
     const float4* __restrict__ rays = j.rays[q];
     const unsigned int lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const unsigned int stride = gridDim.x * SHADE_BLOCK;
@@ -594,6 +594,205 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave2_shade(DScene s, WaveJob j
             if (has_result) j.res[o][e2] = make_float4(result.x, result.y, result.z, 0.0f);
         }
         __syncthreads();                                                            // the next pass of the loop rewrites the shared counters
+    }
+}
+
+// ---- the wavefront over the 8-wide trees (scenes with DScene::wide; hrt_wide.cuh) -----------------------------------------------
+// ONE persistent kernel per iteration replaces k_wave2_secondary + k_wave2_trace: every lane walks its own ray, and a lane
+// whose walk ended takes the next piece of work as soon as fewer than HRT_WIDE_REFILL lanes of its warp are walking —
+//   first a secondary entry of queue q (global hand-out counter; its record goes to hits[entry]),
+//   then the next sample of ITS pixel of the warp's claim (an 8x4 tile x CLAIM3_SPP samples): the camera ray is generated
+//   (K1), settled on the spot when it cannot reach the scene bounds, walked otherwise;  miss -> background + film sum in
+//   shared memory (K4/K5), hit -> appended behind the secondary entries (warp ballot + one atomic, K3) for the shade pass.
+// The lanes of a warp are therefore at different samples of their pixels; a claim ends when every lane has used its samples.
+// Walks advance in phases (hrt_wide.cuh): no instruction of the node / leaf / entry code runs for a handful of lanes while
+// the rest of the warp waits, which is what the lock-step k_wave2_trace did on every scene whose camera rays mostly miss
+// (shiny_teapot: 15 % of the lanes walked while 85 % waited).  Rays that need pass 2 get a pending record and are listed in
+// WaveJob::pend; k_wave3_resolve settles them before the shade pass.  Integer film: same bits as every other pipeline.
+#ifndef HRT_CLAIM3_SPP
+#define HRT_CLAIM3_SPP 8
+#endif
+#ifndef HRT_WAVE3_MIN_BLOCKS
+#define HRT_WAVE3_MIN_BLOCKS 4
+#endif
+constexpr int CLAIM3_SPP = HRT_CLAIM3_SPP;
+constexpr int CLAIM3 = 32 * CLAIM3_SPP;
+
+__host__ __device__ inline unsigned int wave3_sblocks(const WaveJob& j) { return ((unsigned int)j.s_count + CLAIM3_SPP - 1u) / CLAIM3_SPP; }
+
+// per-thread film sums of the current claim in shared memory: lanes q[0..2] fixed point, [3] flag fields (hrt_shade.cuh)
+struct SmemAcc {
+    long long* base;        // &mem[threadIdx.x]; entry k at base[k * BLOCK]
+    __device__ __forceinline__ void clear() { base[0] = 0; base[BLOCK] = 0; base[2 * BLOCK] = 0; base[3 * BLOCK] = 0; }
+    __device__ __forceinline__ void add(V3 c)
+    {
+        const float v[3] = {c.x, c.y, c.z};
+        unsigned long long flags = 0;
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            long long q; unsigned long long flag;
+            film_quantize(v[ch], ch, q, flag);
+            if (q != 0) base[ch * BLOCK] += q;
+            flags |= flag;
+        }
+        if (flags) base[3 * BLOCK] |= (long long)flags;
+    }
+    __device__ __forceinline__ void flush(long long* film, int pix)
+    {
+        long long* px = film + (size_t)pix * FILM_LANES;
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) { const long long q = base[ch * BLOCK]; if (q != 0) atomicAdd((unsigned long long*)(px + ch), (unsigned long long)q); }
+        const long long f = base[3 * BLOCK];
+        if (f) atomicOr((unsigned long long*)(px + 3), (unsigned long long)f);
+        clear();
+    }
+};
+
+template <bool LENS>
+__global__ void __launch_bounds__(BLOCK, HRT_WAVE3_MIN_BLOCKS) k_wave3_trace(DScene s, WaveJob j, DCamera cam, int q)
+{
+    __shared__ int stack_mem[WIDE_STACK * BLOCK];
+    __shared__ long long acc_mem[4 * BLOCK];
+    WideSmemStack<BLOCK> st; st.base = stack_mem + threadIdx.x; st.sp = 0;
+    SmemAcc acc; acc.base = acc_mem + threadIdx.x; acc.clear();
+    WaveCtl* c = j.ctl;
+    const unsigned int n_sec = c->n_front[q];
+    const unsigned long long total_claims = c->total_paths;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { c->rays += n_sec; c->n_front[q ^ 1] = 0; }   // nobody reads these in this kernel
+    const unsigned int lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
+    const unsigned int warps_total = gridDim.x * (BLOCK / 32);
+    const unsigned int room = j.capacity - n_sec;                                 // slots left for camera-path hits
+    const unsigned int margin = warps_total * (unsigned int)CLAIM3;               // what the other warps may still append after a check
+    const unsigned int n_units = wave2_units(j);
+    float4* __restrict__ rays = j.rays[q];
+    PendList pend; pend.idx = j.pend; pend.count = &c->pend_count;
+
+    WideLane L; L.live = false;
+    int kind = 0;                       // what this lane's ray is: 0 none, 1 secondary entry, 2 camera path
+    unsigned int e_idx = 0, r_st = 0; int r_pix = 0;        // the ray's queue entry (secondary) / pixel and packed state
+    int c_pix = -1, c_sl = 0, c_left = 0;                   // the warp's claim: this lane's pixel, its next sample, samples left
+    bool sec_done = n_sec == 0, cam_done = false;           // warp-uniform: nothing more to fetch from that source
+    for (;;) {
+        int walking = __popc(__ballot_sync(0xffffffffu, L.live));
+        if (walking < ((sec_done && cam_done) ? 1 : HRT_WIDE_REFILL)) {
+            // ---- retire the walks that ended
+            const bool fin = kind != 0 && !L.live;
+            Hit h; h.t = 0.0f; h.prim = HRT_MISS; h.obj = -1; h.flags = 0;
+            if (fin) h = wide_result(L);
+            if (fin && kind == 1) {
+                j.hits[e_idx] = h;
+                if (h.flags & HIT_PENDING) pend_push(pend, e_idx);
+                kind = 0;
+            }
+            const bool keep = fin && kind == 2 && (h.prim != HRT_MISS || (h.flags & HIT_PENDING));
+            if (fin && kind == 2 && !keep) {                                        // main.cpp:47-59: the path ends on the background
+                const Ray wr = L.r;
+                const V3 bg = background_colour(s, wr);
+                if (r_pix == c_pix) acc.add(bg); else film_add(j.film, r_pix, bg);   // (a ray of the previous claim)
+                kind = 0;
+            }
+            const unsigned int m_keep = __ballot_sync(0xffffffffu, keep);
+            if (m_keep) {
+                unsigned int e0 = 0;
+                if (lane == 0) e0 = atomicAdd(&c->n_prim[q], (unsigned int)__popc(m_keep));
+                e0 = __shfl_sync(0xffffffffu, e0, 0);
+                if (keep) {
+                    const unsigned int e = n_sec + e0 + (unsigned int)__popc(m_keep & below);
+                    rays[2 * (size_t)e] = make_float4(L.r.o.x, L.r.o.y, L.r.o.z, __int_as_float(r_pix));
+                    rays[2 * (size_t)e + 1] = make_float4(L.r.d.x, L.r.d.y, L.r.d.z, __uint_as_float(r_st));
+                    j.hits[e] = h;
+                    if (h.flags & HIT_PENDING) pend_push(pend, e);
+                    kind = 0;
+                }
+            }
+            // ---- fetch: secondary entries first, then camera paths, until enough lanes walk or nothing can be fetched
+            for (;;) {
+                if (!sec_done) {
+                    const unsigned int m = __ballot_sync(0xffffffffu, kind == 0);
+                    if (m) {
+                        unsigned int base = 0;
+                        if (lane == (unsigned int)(__ffs(m) - 1)) base = atomicAdd(&c->sec_next[q], (unsigned int)__popc(m));
+                        base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+                        const unsigned int my = base + (unsigned int)__popc(m & below);
+                        if (kind == 0 && my < n_sec) {
+                            const float4 a = rays[2 * (size_t)my], b = rays[2 * (size_t)my + 1];
+                            Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
+                            r_pix = __float_as_int(a.w); r_st = __float_as_uint(b.w); e_idx = my; kind = 1;
+                            Hit early; st.sp = 0;
+                            if (!wide_begin(L, s, r, j.t_min, hrt_inf(), early)) { L.b.t = early.t; L.b.prim = early.prim; L.b.obj = early.obj; }
+                        }
+                        if (base + (unsigned int)__popc(m) >= n_sec) sec_done = true;
+                    }
+                }
+                if (!cam_done || __any_sync(0xffffffffu, c_left > 0)) {
+                    if (!__any_sync(0xffffffffu, c_left > 0)) {                         // the claim is used up: the next one
+                        if (c_pix >= 0) acc.flush(j.film, c_pix);
+                        c_pix = -1;
+                        unsigned long long k0 = 0;
+                        if (lane == 0 && ld_relaxed(&c->n_prim[q]) + margin <= room && ld_relaxed(&c->next_path) < total_claims)
+                            k0 = atomicAdd(&c->next_path, 1ull) + 1ull;
+                        k0 = __shfl_sync(0xffffffffu, k0, 0);
+                        if (k0 == 0 || k0 - 1ull >= total_claims) cam_done = true;
+                        else {
+                            const unsigned int k = (unsigned int)(k0 - 1ull);
+                            const unsigned int sb = k / n_units, unit = k - sb * n_units;    // claims of one sample block sweep the film
+                            c_sl = (int)sb * CLAIM3_SPP;
+                            c_left = j.s_count - c_sl < CLAIM3_SPP ? j.s_count - c_sl : CLAIM3_SPP;
+                            if (j.tiles_x > 0) {
+                                const int x = (int)(unit % (unsigned int)j.tiles_x) * 8 + (int)(lane & 7u);
+                                const int y = (int)(unit / (unsigned int)j.tiles_x) * 4 + (int)(lane >> 3);
+                                c_pix = y * j.width + x;
+                            } else {
+                                const unsigned int pp = unit * 32u + lane;
+                                c_pix = pp < (unsigned int)j.npix ? (int)pp : -1;
+                            }
+                            if (c_pix < 0) c_left = 0;
+                        }
+                    }
+                    if (kind == 0 && c_left > 0) {                                   // this lane's next sample (main.cpp:115-123)
+                        const int x = c_pix % j.width, y = c_pix / j.width;
+                        const RngKey key = make_key(j.seed, (uint32_t)c_pix, (uint32_t)(j.s_first + c_sl), j.rng_mode);
+                        const Ray r = primary_ray_xy<LENS>(cam, j.width, j.height, x, j.height - y, key);
+                        r_pix = c_pix; r_st = pack_state(c_sl, 0, false);
+                        ++c_sl; --c_left;
+                        if (s.has_bounds && camera_ray_clears_scene(s, r, j.t_min)) acc.add(background_colour(s, r));
+                        else {
+                            Hit early; st.sp = 0; kind = 2;
+                            if (!wide_begin(L, s, r, j.t_min, hrt_inf(), early)) { L.r = r; L.b.t = early.t; L.b.prim = early.prim; L.b.obj = early.obj; }
+                        }
+                    }
+                }
+                walking = __popc(__ballot_sync(0xffffffffu, L.live));
+                if (walking >= HRT_WIDE_REFILL) break;
+                const bool more_cam = !cam_done || __any_sync(0xffffffffu, c_left > 0);
+                // camera work can only be fetched by idle lanes that still have samples, or by a new claim once every lane is out of samples
+                const bool cam_possible = more_cam && (__any_sync(0xffffffffu, kind == 0 && c_left > 0) || !__any_sync(0xffffffffu, c_left > 0));
+                if (!(!sec_done && __any_sync(0xffffffffu, kind == 0)) && !cam_possible) break;
+            }
+        }
+        const RngKey key = make_key(j.seed, (uint32_t)r_pix, (uint32_t)(j.s_first + (int)((r_st >> 8) & 0x7fffffu)), j.rng_mode);
+        if (!wide_round(L, s, st, key, r_st & 0xffu)) {
+            if (sec_done && cam_done && !__any_sync(0xffffffffu, kind != 0)) break;
+        }
+    }
+    if (c_pix >= 0) acc.flush(j.film, c_pix);
+}
+
+// pass 2 of the entries k_wave3_trace left pending (ties, badly conditioned triangles, NaNs: hrt_trace.cuh), before the shade pass
+__global__ void __launch_bounds__(BLOCK) k_wave3_resolve(DScene s, WaveJob j, int q)
+{
+    WaveCtl* c = j.ctl;
+    const unsigned int n = c->pend_count;
+    const float4* __restrict__ rays = j.rays[q];
+    for (unsigned int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const unsigned int e = j.pend[k];
+        const float4 a = rays[2 * (size_t)e], b = rays[2 * (size_t)e + 1];
+        Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
+        const unsigned int stt = __float_as_uint(b.w);
+        const RngKey key = make_key(j.seed, (uint32_t)__float_as_int(a.w), (uint32_t)(j.s_first + (int)((stt >> 8) & 0x7fffffu)), j.rng_mode);
+        const Hit h = wide_resolve(s, r, j.t_min, hrt_inf(), key, stt & 0xffu, j.hits[e]);
+        if (h.flags & (HIT_RESOLVED | HIT_FALLBACK)) atomicAdd((h.flags & HIT_FALLBACK) ? &c->fallbacks : &c->resolved, 1ull);
+        j.hits[e] = h;
     }
 }
 
@@ -691,6 +890,18 @@ void launch_wave2_trace(const DScene& s, const WaveJob& j, const DCamera& cam, i
         else k_wave2_trace<4, false><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
     }
     *launches += 1;
+}
+unsigned long long wave3_total_claims(const WaveJob& j) { return (unsigned long long)wave2_units(j) * (unsigned long long)wave3_sblocks(j); }
+void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, int sm_count, cudaStream_t st, uint64_t* launches)
+{
+    long long cap = (long long)j.capacity / (4ll * CLAIM3 * (BLOCK / 32));          // keeps the append margin below 1/4 of the queue
+    long long want = (long long)sm_count * HRT_WAVE3_MIN_BLOCKS;                    // one resident wave: the warps loop until the work is gone
+    if (cap < 1) cap = 1;
+    const int blocks = (int)(want < cap ? want : cap);
+    if (cam.lens_radius > 0.0f) k_wave3_trace<true><<<blocks, BLOCK, 0, st>>>(s, j, cam, it & 1);
+    else k_wave3_trace<false><<<blocks, BLOCK, 0, st>>>(s, j, cam, it & 1);
+    k_wave3_resolve<<<sm_count * 2, BLOCK, 0, st>>>(s, j, it & 1);
+    *launches += 2;
 }
 void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches)
 {

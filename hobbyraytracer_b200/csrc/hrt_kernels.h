@@ -22,6 +22,8 @@ struct WaveCtl {
     unsigned long long fallbacks;       // rays answered by trace_ref
     unsigned int sec_next[2];           // fused-primary pipeline: hand-out counter of the secondary entries of queue q (per-lane refill)
     unsigned int n_prim[2];             // fused-primary pipeline: camera-path hits appended behind the n_front[q] secondary entries of queue q
+    unsigned int pend_count;            // wide pipeline: entries of the current queue whose hit record is pending (WaveJob::pend), reset by the shade pass
+    unsigned int pad_;
     float dbg[16][8];                   // first rays that took the trace_ref fallback (o, pixel, d, state), for diagnosis
 };
 
@@ -44,6 +46,7 @@ struct WaveJob {
     float4* thr[2];
     float4* res[2];
     Hit* hits;
+    unsigned int* pend;                 // capacity entry indices: rays pass 1 could not decide (hrt_wide.cuh), settled by the resolve pass
     WaveCtl* ctl;
     long long* film;                    // npix * FILM_LANES
 };
@@ -63,6 +66,10 @@ void launch_wave_shade(const DScene& s, const WaveJob& j, const DCamera& cam, in
 // + shade2(queue it&1 -> survivors to queue (it+1)&1); no init pass, the control block starts zeroed with total_paths set
 unsigned long long wave2_total_claims(const WaveJob& j);   // value of WaveCtl::total_paths for this pipeline (it hands out claims, not paths)
 void launch_wave2_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, bool secondary_heavy, int sm_count, cudaStream_t st, uint64_t* launches);
+// the same pipeline over the 8-wide trees (scenes with DScene::wide): ONE persistent kernel walks the secondary entries and
+// the camera paths in phases with per-lane refill (hrt_wide.cuh), a small second kernel settles the pending entries
+unsigned long long wave3_total_claims(const WaveJob& j);
+void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches);
 // one thread per path, whole rayColour loop (validation of the wavefront pipeline); same film
 void launch_render_mega(const DScene& s, const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches);

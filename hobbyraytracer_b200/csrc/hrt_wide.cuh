@@ -214,6 +214,30 @@ template <class St> HRT_HD void wide_node_step(WideLane& L, const DScene& s, St&
     if (L.b.bad) L.live = false;
 }
 
+// itriangle_t<3> (hrt_trace.cuh) without early exits: the same operations in the same order on every lane, the verdict formed at
+// the end with non-short-circuit logic, so the lanes of a leaf phase stay together (r2b profile: the early exits left 5.5 of
+// 32 lanes in the second half of the test).  A rejected triangle's t is garbage and never read.
+HRT_HD bool wide_itriangle(const float4& P0, const float4& P1, const float4& P2, const TriRay& q, float t_max, float& t)
+{
+    V3 p0t = permute<3>(xyz(P0) - q.o, q.kz), p1t = permute<3>(xyz(P1) - q.o, q.kz), p2t = permute<3>(xyz(P2) - q.o, q.kz);
+    p0t.x += q.sX * p0t.z; p0t.y += q.sY * p0t.z;
+    p1t.x += q.sX * p1t.z; p1t.y += q.sY * p1t.z;
+    p2t.x += q.sX * p2t.z; p2t.y += q.sY * p2t.z;
+    const float e0 = p1t.x * p2t.y - p1t.y * p2t.x;
+    const float e1 = p2t.x * p0t.y - p2t.y * p0t.x;
+    const float e2 = p0t.x * p1t.y - p0t.y * p1t.x;
+    const bool mixed = ((e0 < 0) | (e1 < 0) | (e2 < 0)) & ((e0 > 0) | (e1 > 0) | (e2 > 0));
+    const float det = e0 + e1 + e2;
+    p0t.z *= q.sZ; p1t.z *= q.sZ; p2t.z *= q.sZ;
+    const float tScaled = e0 * p0t.z + e1 * p1t.z + e2 * p2t.z;
+    const float lim = t_max * det;
+    const bool out_neg = (det < 0) & ((tScaled >= 0) | (tScaled < lim));
+    const bool out_pos = (det > 0) & ((tScaled <= 0) | (tScaled > lim));
+    const float invDet = 1 / det;
+    t = tScaled * invDet;
+    return !mixed & (det != 0) & !out_neg & !out_pos;
+}
+
 // ---- triangle leaf: the 1-2 triangles of a bottom node of the reference topology, exact ITriangle arithmetic; the reference's own
 // slab test of the node box only for a triangle that accepted (world_walk has the reasoning)
 template <class St> HRT_HD void wide_leaf_step(WideLane& L, const DScene& s, St& st)
@@ -226,8 +250,8 @@ template <class St> HRT_HD void wide_leaf_step(WideLane& L, const DScene& s, St&
     const float4 L0 = wide_f4(a.w[0], a.w[1], a.w[2]), L1 = wide_f4(a.w[4], a.w[5], a.w[6]), L2 = wide_f4(b.w[0], b.w[1], b.w[2]);
     const float4 R0 = wide_f4(b.w[4], b.w[5], b.w[6]), R1 = wide_f4(c.w[0], c.w[1], c.w[2]), R2 = wide_f4(c.w[4], c.w[5], c.w[6]);
     float tL = 0, tR = 0;
-    const bool hL = itriangle_t<3>(L0, L1, L2, L.tq, bound, tL);
-    const bool hR = triR != triL && itriangle_t<3>(R0, R1, R2, L.tq, bound, tR);
+    const bool hL = wide_itriangle(L0, L1, L2, L.tq, bound, tL);
+    const bool hR = wide_itriangle(R0, R1, R2, L.tq, bound, tR) & (triR != triL);
     if (hL || hR) {
         const W32 box = wide_ld32(R);
         Ray lr; lr.o = L.q.o; lr.d = L.ld;

@@ -269,7 +269,8 @@ int   hrt_film_resolve_peers(hrt_scene* s, void* d_film, const void* peer_handle
 
 /* Introspection of a committed scene (tests, tooling): copies one device array of mesh `mesh_index` (world-list order of
  * first use) into `out` (may be NULL) and returns its size in bytes.  which: 0 reference-topology nodes (32 B each),
- * 1 fast-tree nodes (64 B), 2 leaf records (128 B), 3 triangle positions (48 B), 4 triangle attributes (64 B). */
+ * 1 fast-tree nodes (64 B), 2 leaf records (128 B), 3 triangle positions (48 B), 4 triangle attributes (64 B),
+ * 5 nodes of the 8-wide tree the render kernels walk (96 B). */
 int64_t hrt_scene_mesh_array(hrt_scene* s, int mesh_index, int which, void* out, int64_t capacity_bytes);
 
 int hrt_get_stats(hrt_scene* s, hrt_stats* out);

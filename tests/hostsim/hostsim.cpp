@@ -229,11 +229,12 @@ int64_t hsim_mesh_bvh_nodes(hsim_scene* s, int shape, float* boxes, int32_t* chi
 // the arrays hrt_scene_mesh_array returns, from the host builder (HRT_BVH_LBVH_HOST is the mirror of the device builder)
 int64_t hsim_scene_mesh_array(hsim_scene* s, int mesh_index, int which, void* out, int64_t capacity)
 {
-    if (mesh_index < 0 || (size_t)mesh_index >= s->host.mesh_shapes.size() || which < 0 || which > 4) { g_err = "bad argument"; return HRT_ERR_ARG; }
+    if (mesh_index < 0 || (size_t)mesh_index >= s->host.mesh_shapes.size() || which < 0 || which > 5) { g_err = "bad argument"; return HRT_ERR_ARG; }
     const HostShape& sh = s->host.shapes[(size_t)s->host.mesh_shapes[(size_t)mesh_index]];
     const std::vector<float4>* src[5] = {&sh.ref.nodes, &sh.fast.nodes, &sh.leaves, &sh.tris4, &sh.attrs4};
-    const int64_t bytes = (int64_t)(src[which]->size() * sizeof(float4));
-    if (out) { if (capacity < bytes) { g_err = "buffer too small"; return HRT_ERR_ARG; } if (bytes) std::memcpy(out, src[which]->data(), (size_t)bytes); }
+    const void* data = which == 5 ? (const void*)sh.wide.nodes.data() : (const void*)src[which]->data();
+    const int64_t bytes = which == 5 ? (int64_t)(sh.wide.nodes.size() * sizeof(WNode)) : (int64_t)(src[which]->size() * sizeof(float4));
+    if (out) { if (capacity < bytes) { g_err = "buffer too small"; return HRT_ERR_ARG; } if (bytes) std::memcpy(out, data, (size_t)bytes); }
     return bytes;
 }
 } // extern "C"

@@ -126,3 +126,46 @@ def test_teapot_scene_wide(orc, hsim, cache_dir):
     same(ro, rw)
     two = h.trace(rays, extras=False)
     same(ro, two)
+
+
+@pytest.mark.parametrize("mode", [abi.BVH_SAH, abi.BVH_LBVH_HOST])
+def test_wide_collapse_structure(hsim, mode):
+    """hrt_bvh_rules.h (4): every leaf record is reachable exactly once, wide nodes are numbered breadth first (the children
+    of node i come after i, in slot order), and the quantised box of a child contains everything below it."""
+    sd = mesh_scene(40, with_floor=False)
+    h = sd.build(hsim, mode, 3)
+    leaves = h.mesh_array(0, 2).reshape(-1, 32)
+    raw = h.mesh_array(0, 5).view(np.uint8).reshape(-1, 96)
+    n = raw.shape[0]
+    p = raw[:, 0:12].copy().view(F).reshape(n, 3).astype(np.float64)
+    meta = raw[:, 12:16].copy().view(np.uint32).reshape(n)
+    q = raw[:, 16:64].reshape(n, 6, 8).astype(np.float64)
+    child = raw[:, 64:96].copy().view(np.int32).reshape(n, 8)
+    step = np.stack([np.ldexp(1.0, ((meta >> (8 * a)) & 0xff).astype(np.int64) - 127) for a in range(3)], 1)      # n x 3
+    valid = (meta >> 24) & 0xff
+    lo = p[:, :, None] + q[:, 0::2, :] * step[:, :, None]          # n x 3 x 8
+    hi = p[:, :, None] + q[:, 1::2, :] * step[:, :, None]
+    seen = np.zeros(leaves.shape[0], np.int64)
+    nxt = 1
+    sub_lo = np.full((n, 3), np.inf); sub_hi = np.full((n, 3), -np.inf)       # true bounds of everything below node i
+    order = []
+    for i in range(n):
+        for s in range(8):
+            if not (valid[i] >> s) & 1:
+                continue
+            c = child[i, s]
+            if c >= 0:
+                assert c == nxt, "breadth-first numbering in slot order"
+                nxt += 1
+            else:
+                seen[~c] += 1
+            order.append((i, s, c))
+    assert nxt == n and (seen == 1).all()
+    for i, s, c in reversed(order):                                            # children have larger indices: one backwards sweep
+        if c >= 0:
+            blo, bhi = sub_lo[c], sub_hi[c]
+        else:
+            blo, bhi = leaves[~c, 0:3].astype(np.float64), leaves[~c, 4:7].astype(np.float64)
+        assert (lo[i, :, s] <= blo).all() and (hi[i, :, s] >= bhi).all(), (i, s, c)
+        sub_lo[i] = np.minimum(sub_lo[i], blo); sub_hi[i] = np.maximum(sub_hi[i], bhi)
+        assert (hi[i, :, s] - lo[i, :, s] <= (bhi - blo) + 2.0 * step[i] + 1e-30).all(), "quantisation adds at most one grid step per side"

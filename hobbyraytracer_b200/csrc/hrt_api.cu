@@ -268,7 +268,8 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
     cudaEvent_t ev_begin = s->events[EV_PER_CHUNK * CTL_RING], ev_end = s->events[EV_PER_CHUNK * CTL_RING + 1];
 
     const bool wide = s->d.wide && !mega && !v1 && !getenv("HRT_NO_WIDE");     // the pipeline over the 8-wide trees (hrt_wide.cuh)
-    WaveCtl init{}; init.total_paths = (mega || v1) ? total : (wide ? wave3_total_claims(j) : wave2_total_claims(j));
+    const bool merged = wide && getenv("HRT_WAVE3_MERGED");                   // A/B: camera paths in the phase kernel too
+    WaveCtl init{}; init.total_paths = (mega || v1) ? total : (merged ? wave3_total_claims(j) : wave2_total_claims(j));
     CK(cudaMemcpyAsync(j.ctl, &init, sizeof(init), cudaMemcpyHostToDevice, st));
     CK(cudaEventRecord(ev_begin, st));
     s->stats.paths += total;
@@ -303,7 +304,7 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
             for (int k = 0; k < CHUNK; ++k, ++it) {
                 CK(cudaEventRecord(ev[2 * k], st));
                 if (v1) launch_wave_trace(s->d, j, it, s->sm_count, st, &s->stats.launches);
-                else if (wide) launch_wave3_trace(s->d, j, dc, it, s->sm_count, st, &s->stats.launches);
+                else if (wide) launch_wave3_trace(s->d, j, dc, it, secondary_heavy, merged, s->sm_count, st, &s->stats.launches);
                 else launch_wave2_trace(s->d, j, dc, it, secondary_heavy, s->sm_count, st, &s->stats.launches);
                 CK(cudaEventRecord(ev[2 * k + 1], st));
                 if (v1) launch_wave_shade(s->d, j, dc, it, s->sm_count, st, &s->stats.launches);

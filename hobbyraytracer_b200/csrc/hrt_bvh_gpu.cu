@@ -442,7 +442,7 @@ bool build_mesh_gpu(const MeshSource& src, int64_t n_tri, uint64_t seed, int sha
 
     DMesh& m = out.mesh;
     m.ref_nodes = d_ref; m.tris = d_tris; m.attrs = d_attrs; m.fast_nodes = d_fast; m.fast_leaves = d_leaves;
-    m.wide_nodes = wide_bad ? nullptr : d_wide; m.wide_root = fast_root;      // wide_bad: boxes off the 8-bit grids - the scene keeps to the two-child walk
+    m.wide_nodes = (wide_bad || n_wide >= (size_t(1) << 24)) ? nullptr : d_wide; m.wide_root = fast_root;      // wide_bad: boxes off the 8-bit grids - the scene keeps to the two-child walk
     m.ref_root = 0; m.fast_root = fast_root; m.n_tri = n_tri;
     out.n_wide_nodes = n_wide; out.wide_depth = wide_depth;
     out.n_ref_nodes = n_nodes; out.n_fast_nodes = n_leaves > 1 ? n_leaves - 1 : 0; out.n_leaves = n_leaves;

@@ -468,7 +468,7 @@ void build_wide(const FastBvh& fast, WideBvh& out)
         });
         base = next_base; level.swap(next);
     }
-    out.root = 0; out.ok = ok;
+    out.root = 0; out.ok = ok && out.nodes.size() < (size_t(1) << 24);       // stack entries carry a node index in 24 bits (hrt_wide.cuh)
 }
 
 // ------------------------------------------------------------------------------------------------------------

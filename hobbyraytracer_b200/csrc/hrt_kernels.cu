@@ -597,6 +597,57 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave2_shade(DScene s, WaveJob j
     }
 }
 
+// ---- secondary rays of queue q over the 8-wide trees (scenes with DScene::wide) --------------------------------------------------
+// Persistent warps, per-lane refill from the queue's hand-out counter, phases (hrt_wide.cuh); records go to hits[entry], rays
+// that need pass 2 to WaveJob::pend (k_wave3_resolve).  Runs before k_wave2_trace, which is told to skip these entries.
+#ifndef HRT_WSEC_MIN_BLOCKS
+#define HRT_WSEC_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(BLOCK, HRT_WSEC_MIN_BLOCKS) k_wide_secondary(DScene s, WaveJob j, int q)
+{
+    __shared__ int stack_mem[WIDE_STACK * BLOCK];
+    WaveCtl* c = j.ctl;
+    const unsigned int n_sec = c->n_front[q];
+    if (n_sec == 0) return;
+    WideSmemStack<BLOCK> st; st.base = stack_mem + threadIdx.x; st.sp = 0;
+    const unsigned int lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
+    const float4* __restrict__ rays = j.rays[q];
+    PendList pend; pend.idx = j.pend; pend.count = &c->pend_count;
+    WideLane L; L.live = false;
+    bool have = false, exhausted = false;
+    unsigned int e_idx = 0, r_st = 0; int r_pix = 0;
+    for (;;) {
+        const int walking = __popc(__ballot_sync(0xffffffffu, L.live));
+        if (walking < (exhausted ? 1 : HRT_WIDE_REFILL)) {
+            if (have && !L.live) {
+                const Hit h = wide_result(L);
+                j.hits[e_idx] = h;
+                if (h.flags & HIT_PENDING) pend_push(pend, e_idx);
+                have = false;
+            }
+            if (!exhausted) {
+                const unsigned int m = __ballot_sync(0xffffffffu, !have);
+                unsigned int base = 0;
+                if (lane == (unsigned int)(__ffs(m) - 1)) base = atomicAdd(&c->sec_next[q], (unsigned int)__popc(m));
+                base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+                const unsigned int my = base + (unsigned int)__popc(m & below);
+                if (!have && my < n_sec) {
+                    const float4 a = rays[2 * (size_t)my], b = rays[2 * (size_t)my + 1];
+                    Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
+                    r_pix = __float_as_int(a.w); r_st = __float_as_uint(b.w); e_idx = my; have = true;
+                    Hit early; st.sp = 0;
+                    if (!wide_begin(L, s, r, j.t_min, hrt_inf(), early)) { L.b.t = early.t; L.b.prim = early.prim; L.b.obj = early.obj; }
+                }
+                if (base + (unsigned int)__popc(m) >= n_sec) exhausted = true;
+            }
+        }
+        const RngKey key = make_key(j.seed, (uint32_t)r_pix, (uint32_t)(j.s_first + (int)((r_st >> 8) & 0x7fffffu)), j.rng_mode);
+        if (!wide_round(L, s, st, key, r_st & 0xffu) && exhausted) {
+            if (!__any_sync(0xffffffffu, have)) break;
+        }
+    }
+}
+
 // ---- the wavefront over the 8-wide trees (scenes with DScene::wide; hrt_wide.cuh) -----------------------------------------------
 // ONE persistent kernel per iteration replaces k_wave2_secondary + k_wave2_trace: every lane walks its own ray, and a lane
 // whose walk ended takes the next piece of work as soon as fewer than HRT_WIDE_REFILL lanes of its warp are walking —
@@ -892,16 +943,32 @@ void launch_wave2_trace(const DScene& s, const WaveJob& j, const DCamera& cam, i
     *launches += 1;
 }
 unsigned long long wave3_total_claims(const WaveJob& j) { return (unsigned long long)wave2_units(j) * (unsigned long long)wave3_sblocks(j); }
-void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, int sm_count, cudaStream_t st, uint64_t* launches)
+void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, bool secondary_heavy, bool merged, int sm_count, cudaStream_t st, uint64_t* launches)
 {
-    long long cap = (long long)j.capacity / (4ll * CLAIM3 * (BLOCK / 32));          // keeps the append margin below 1/4 of the queue
-    long long want = (long long)sm_count * HRT_WAVE3_MIN_BLOCKS;                    // one resident wave: the warps loop until the work is gone
-    if (cap < 1) cap = 1;
-    const int blocks = (int)(want < cap ? want : cap);
-    if (cam.lens_radius > 0.0f) k_wave3_trace<true><<<blocks, BLOCK, 0, st>>>(s, j, cam, it & 1);
-    else k_wave3_trace<false><<<blocks, BLOCK, 0, st>>>(s, j, cam, it & 1);
+    if (merged) {                                                                   // A/B: secondary entries and camera paths in one phase kernel
+        long long cap = (long long)j.capacity / (4ll * CLAIM3 * (BLOCK / 32));      // keeps the append margin below 1/4 of the queue
+        long long want = (long long)sm_count * HRT_WAVE3_MIN_BLOCKS;                // one resident wave: the warps loop until the work is gone
+        if (cap < 1) cap = 1;
+        const int blocks = (int)(want < cap ? want : cap);
+        if (cam.lens_radius > 0.0f) k_wave3_trace<true><<<blocks, BLOCK, 0, st>>>(s, j, cam, it & 1);
+        else k_wave3_trace<false><<<blocks, BLOCK, 0, st>>>(s, j, cam, it & 1);
+        *launches += 1;
+    } else {
+        // secondary rays: phase kernel over the wide trees; camera paths: the lock-step fused-primary kernel (most of them are settled by
+        // the scene-bounds test and the rest is coherent, which the lock-step walk handles well)
+        k_wide_secondary<<<sm_count * HRT_WSEC_MIN_BLOCKS, BLOCK, 0, st>>>(s, j, it & 1);
+        const bool lens = cam.lens_radius > 0.0f;
+        if (secondary_heavy) {
+            if (lens) k_wave2_trace<8, true><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, 1);
+            else k_wave2_trace<8, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, 1);
+        } else {
+            if (lens) k_wave2_trace<4, true><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, 1);
+            else k_wave2_trace<4, false><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, 1);
+        }
+        *launches += 2;
+    }
     k_wave3_resolve<<<sm_count * 2, BLOCK, 0, st>>>(s, j, it & 1);
-    *launches += 2;
+    *launches += 1;
 }
 void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches)
 {

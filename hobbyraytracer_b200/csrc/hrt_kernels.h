@@ -69,7 +69,7 @@ void launch_wave2_trace(const DScene& s, const WaveJob& j, const DCamera& cam, i
 // the same pipeline over the 8-wide trees (scenes with DScene::wide): ONE persistent kernel walks the secondary entries and
 // the camera paths in phases with per-lane refill (hrt_wide.cuh), a small second kernel settles the pending entries
 unsigned long long wave3_total_claims(const WaveJob& j);
-void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, int sm_count, cudaStream_t st, uint64_t* launches);
+void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, bool secondary_heavy, bool merged, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches);
 // one thread per path, whole rayColour loop (validation of the wavefront pipeline); same film
 void launch_render_mega(const DScene& s, const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches);

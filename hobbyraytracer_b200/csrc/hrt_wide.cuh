@@ -24,7 +24,7 @@
 
 namespace hrt {
 
-constexpr int WIDE_STACK = 40;                        // stack entries per lane; more pending children than this: pass 2
+constexpr int WIDE_STACK = 32;                        // stack entries per lane (one per node with children left + one per mesh entered); deeper: pass 2
 constexpr float WIDE_WIDEN = 9.5367431640625e-7f;     // 2^-20, relative to |(p - o) / d| + |grid extent / d| (see wide_hits)
 constexpr int HIT_PENDING = 8;                        // Hit::flags: pass 1 could not decide; Hit::t carries the cull bound
 constexpr int PEND_BAD = 16, PEND_SHEAR = 32;         // Hit::flags of a pending entry: arguments of trace_resolve
@@ -35,12 +35,28 @@ HRT_HD W32 wide_ld32(const void* p)
 {
     W32 r;
 #if defined(__CUDA_ARCH__)
-    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
         : "=r"(r.w[0]), "=r"(r.w[1]), "=r"(r.w[2]), "=r"(r.w[3]), "=r"(r.w[4]), "=r"(r.w[5]), "=r"(r.w[6]), "=r"(r.w[7]) : "l"(p));
 #else
     __builtin_memcpy(&r, p, 32);
 #endif
     return r;
+}
+HRT_HD void wide_prefetch(const void* p)          // the sector is wanted in L1 a few hundred cycles from now (a node's child ids)
+{
+#if defined(__CUDA_ARCH__)
+    asm volatile("prefetch.global.L1 [%0];" :: "l"(p));
+#else
+    (void)p;
+#endif
+}
+HRT_HD int wide_ld_child(const WNode* nodes, uint32_t node, uint32_t slot)
+{
+#if defined(__CUDA_ARCH__)
+    return __ldg(&nodes[node].child[slot]);
+#else
+    return nodes[node].child[slot];
+#endif
 }
 HRT_HD uint32_t wide_perm(uint32_t a, uint32_t b, uint32_t sel)
 {
@@ -119,18 +135,8 @@ HRT_HD uint32_t wide_xor_bits(uint32_t m, uint32_t r)
     if (r & 4u) m = ((m & 0xF0u) >> 4) | ((m & 0x0Fu) << 4);
     return m;
 }
-// v[k] <- v[k ^ r]
-HRT_HD void wide_xor_words(uint32_t* v, uint32_t r)
-{
-#define HRT_WSWAP(a, b) { const uint32_t t_ = v[a]; v[a] = v[b]; v[b] = t_; }
-    if (r & 1u) { HRT_WSWAP(0, 1) HRT_WSWAP(2, 3) HRT_WSWAP(4, 5) HRT_WSWAP(6, 7) }
-    if (r & 2u) { HRT_WSWAP(0, 2) HRT_WSWAP(1, 3) HRT_WSWAP(4, 6) HRT_WSWAP(5, 7) }
-    if (r & 4u) { HRT_WSWAP(0, 4) HRT_WSWAP(1, 5) HRT_WSWAP(2, 6) HRT_WSWAP(3, 7) }
-#undef HRT_WSWAP
-}
-
 // ---- one lane's walk ------------------------------------------------------------------------------------------------------------
-// St is the stack: push(int), pop() -> int, empty().  In the kernels it is a column of shared memory; in the CPU simulation
+// St is the stack: push(int) -> false when full, top(), set_top(int), drop(), empty().  In the kernels it is a column of shared memory; in the CPU simulation
 // (tests/hostsim) a plain array.
 struct WideLane {
     Ray r; V3 rid; float t_min;                    // the world ray
@@ -156,13 +162,30 @@ HRT_HD void wide_enter_top(WideLane& L, const DScene& s)
     L.nodes = s.tlas_wide; L.leaves = nullptr; L.prim_base = 0; L.obj = -1;
     wide_set_bound(L);
 }
+// Stack entries are GROUPS: (wide node << 8) | the children of that node still to be walked, as a mask in walking order (bit k
+// = slot k ^ oct; the highest set bit is the nearest octant), or WALK_MARK ("leave the mesh").  One entry per node however many
+// of its children were hit, so the stack never holds more than the depth of the trees; a child's id is read from its node only
+// when it is walked (the sector was prefetched when the node was tested).
+HRT_HD int wide_fls(uint32_t m)
+{
+#if defined(__CUDA_ARCH__)
+    return 31 - __clz((int)m);
+#else
+    return 31 - __builtin_clz(m);
+#endif
+}
 template <class St> HRT_HD void wide_pop(WideLane& L, const DScene& s, St& st)
 {
     for (;;) {
         if (st.empty() || L.b.bad) { L.live = false; return; }
-        const int v = st.pop();
-        if (v != WALK_MARK) { L.cur = v; return; }
-        wide_enter_top(L, s);                                                  // the mesh is done: back to the world ray
+        const uint32_t v = (uint32_t)st.top();
+        if (v == (uint32_t)WALK_MARK) { st.drop(); wide_enter_top(L, s); continue; }     // the mesh is done: back to the world ray
+        uint32_t mp = v & 0xffu; const uint32_t node = v >> 8;
+        const int k = wide_fls(mp);
+        mp &= ~(1u << k);
+        if (mp) st.set_top((int)((node << 8) | mp)); else st.drop();
+        L.cur = wide_ld_child(L.nodes, node, (uint32_t)k ^ L.q.oct);
+        return;
     }
 }
 
@@ -192,26 +215,17 @@ HRT_HD bool wide_begin(WideLane& L, const DScene& s, const Ray& r, float t_min, 
 // ---- node step: tests the eight children of node L.cur, continues with the nearest one (octant order), stacks the others
 template <class St> HRT_HD void wide_node_step(WideLane& L, const DScene& s, St& st)
 {
-    const char* N = (const char*)(L.nodes + (size_t)L.cur);
+    const uint32_t node = (uint32_t)L.cur;
+    const char* N = (const char*)(L.nodes + (size_t)node);
     const W32 c0 = wide_ld32(N), c1 = wide_ld32(N + 32);
-    W32 ch = wide_ld32(N + 64);
+    wide_prefetch(N + 64);
     const float t_lo = fminf(L.t_min, 0.0f);                                    // ITriangle::hit ignores t_min but only reports t > 0
-    uint32_t m = wide_hits(c0, c1, L.q, t_lo, L.bnd0);
-    if (m == 0) { wide_pop(L, s, st); return; }
-    m = wide_xor_bits(m, L.q.oct);
-    wide_xor_words(ch.w, L.q.oct);
-    bool have = false; int cur = 0;
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-    for (int k = 0; k < 8; ++k) {                                               // far to near: the last one found is walked next
-        if (m & (1u << k)) {
-            if (have) { if (!st.push(cur)) L.b.bad = 1; }
-            cur = (int)ch.w[k]; have = true;
-        }
-    }
-    L.cur = cur;
-    if (L.b.bad) L.live = false;
+    uint32_t mp = wide_xor_bits(wide_hits(c0, c1, L.q, t_lo, L.bnd0), L.q.oct);   // walking order: the highest bit is the nearest octant
+    if (mp == 0) { wide_pop(L, s, st); return; }
+    const int k = wide_fls(mp);
+    mp &= ~(1u << k);
+    if (mp && !st.push((int)((node << 8) | mp))) { L.b.bad = 1; L.live = false; return; }
+    L.cur = wide_ld_child(L.nodes, node, (uint32_t)k ^ L.q.oct);
 }
 
 // itriangle_t<3> (hrt_trace.cuh) without early exits: the same operations in the same order on every lane, the verdict formed at
@@ -293,9 +307,15 @@ template <class St> HRT_HD void wide_object_step(WideLane& L, const DScene& s, S
             }
         }
     } else {
-        float t; uint32_t prim;
-        const Ray wr = L.r;                                                     // a copy: hit_object_ref is out of line
-        if (hit_object_ref(s, i, wr, L.t_min, cull_bound(L.b), t, prim, key, bounce)) { consider(L.b, t, t, prim, i); wide_set_bound(L); }
+        float t = 0.0f; uint32_t prim = ob.prim_base; bool hit;
+        const float bound = cull_bound(L.b);
+        if (!ob.medium && ob.xf_count == 0 && ob.kind == SHAPE_SPHERE) hit = sphere_t(ob.f, L.r, L.t_min, bound, t);        // the common entries in line
+        else if (!ob.medium && ob.xf_count == 0 && ob.kind == SHAPE_RECT) { float a, b; hit = rect_t(ob.axis, ob.f[0], ob.f[1], ob.f[2], ob.f[3], ob.f[4], L.r, L.t_min, bound, t, a, b); }
+        else {
+            const Ray wr = L.r;                                                 // a copy: hit_object_ref is out of line
+            hit = hit_object_ref(s, i, wr, L.t_min, bound, t, prim, key, bounce);
+        }
+        if (hit) { consider(L.b, t, t, prim, i); wide_set_bound(L); }
     }
     wide_pop(L, s, st);
 }
@@ -319,7 +339,9 @@ HRT_HD Hit wide_resolve(const DScene& s, const Ray& r, float t_min, float t_max,
 struct WideArrayStack {
     int v[WIDE_STACK]; int sp = 0;
     HRT_HD bool push(int x) { if (sp >= WIDE_STACK) return false; v[sp++] = x; return true; }
-    HRT_HD int pop() { return v[--sp]; }
+    HRT_HD int top() const { return v[sp - 1]; }
+    HRT_HD void set_top(int x) { v[sp - 1] = x; }
+    HRT_HD void drop() { --sp; }
     HRT_HD bool empty() const { return sp == 0; }
 };
 HRT_HDN inline Hit wide_trace_scalar(const DScene& s, const Ray& r, float t_min, float t_max, const RngKey& key, uint32_t bounce, unsigned long long* steps)
@@ -355,7 +377,9 @@ HRT_HDN inline Hit wide_trace_scalar(const DScene& s, const Ray& r, float t_min,
 template <int THREADS> struct WideSmemStack {
     int* base; int sp;
     __device__ __forceinline__ bool push(int x) { if (sp >= WIDE_STACK) return false; base[sp * THREADS] = x; ++sp; return true; }
-    __device__ __forceinline__ int pop() { --sp; return base[sp * THREADS]; }
+    __device__ __forceinline__ int top() const { return base[(sp - 1) * THREADS]; }
+    __device__ __forceinline__ void set_top(int x) { base[(sp - 1) * THREADS] = x; }
+    __device__ __forceinline__ void drop() { --sp; }
     __device__ __forceinline__ bool empty() const { return sp == 0; }
 };
 

@@ -131,6 +131,7 @@ class Lib:
         self._sig("device_count", i, [], required=False)
         self._sig("set_device", i, [i], required=False)
         self._sig("render", i, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp], required=False)
+        self._sig("render_multi", i, [_vp, _vp, i, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp], required=False)
         self._sig("render_progressive", i, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), C.c_char_p, i, PROGRESS_FN, _vp, _vp, _vp], required=False)
         self._sig("checkpoint_samples", i, [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)], required=False)
         self._sig("render_accumulate_device", i, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp], required=False)
@@ -150,7 +151,10 @@ class Lib:
         self._sig("film_resolve", i, [_vp, i, i, i, _vp], required=False)
         self._sig("camera_rays", i, [C.POINTER(Camera), _vp, i64, _vp], required=False)
         self._sig("rng_draw", i, [i, u64, u64, i64, _vp], required=False)
-        self._sig("scatter_batch", i, [_vp, i, _vp, _vp, i64, u64, _vp], required=False)
+        if self.prefix == "hrt_":     # the product's entry also takes the rng mode of hrt_render_params
+            self._sig("scatter_batch", i, [_vp, i, _vp, _vp, i64, u64, i, _vp], required=False)
+        else:
+            self._sig("scatter_batch", i, [_vp, i, _vp, _vp, i64, u64, _vp], required=False)
         self._sig("texture_eval", i, [_vp, i, _vp, i64, _vp], required=False)
         self._sig("mesh_bvh_nodes", i64, [_vp, i, _vp, _vp], required=False)
         self._sig("scene_mesh_array", i64, [_vp, i, i, _vp, i64], required=False)
@@ -365,6 +369,15 @@ class Scene:
         self.lib.check(self.lib.fn("render")(self.h, C.byref(cam), C.byref(p), _ptr(s), _ptr(b)), "render")
         return s, b
 
+    def render_multi(self, devices, cam: Camera, width: int, height: int, spp: int, seed: int = 1, max_depth: int = 50, t_min: float = 0.001,
+                     rng_mode: int = 0, flags: int = 0):
+        """hrt_render_multi: one process, the GPUs in `devices` (devices[0] = the scene's own) -> (sum, rgb8)"""
+        p = RenderParams(width, height, spp, 0, 0, max_depth, t_min, seed, rng_mode, flags)
+        d = (C.c_int * len(devices))(*devices)
+        s = np.empty((height, width, 3), np.float32); b = np.empty((height, width, 3), np.uint8)
+        self.lib.check(self.lib.fn("render_multi")(self.h, d, len(devices), C.byref(cam), C.byref(p), _ptr(s), _ptr(b)), "render_multi")
+        return s, b
+
     def render_progressive(self, cam: Camera, width: int, height: int, spp: int, seed: int = 1, checkpoint: Optional[str] = None,
                            slice_spp: int = 0, on_slice=None, max_depth: int = 50, t_min: float = 0.001, rng_mode: int = 0, flags: int = 0):
         """hrt_render_progressive -> (rc, sum, rgb8); rc 1 = stopped by on_slice(samples_done, spp) returning non-zero."""
@@ -406,10 +419,13 @@ class Scene:
         self.lib.check(self.lib.fn("render_f32_defocus")(self.h, C.byref(cam), width, height, spp, seed, threads, _ptr(s), C.byref(rays)), "render_f32_defocus")
         return s, int(rays.value)
 
-    def scatter(self, material: int, inputs: np.ndarray, front: np.ndarray, seed: int = 0) -> np.ndarray:
+    def scatter(self, material: int, inputs: np.ndarray, front: np.ndarray, seed: int = 0, rng_mode: int = 0) -> np.ndarray:
         inputs = _f32(inputs).reshape(-1, 14); front = np.ascontiguousarray(front, np.uint8)
         out = np.empty((inputs.shape[0], 10), np.float32)
-        self.lib.check(self.lib.fn("scatter_batch")(self.h, material, _ptr(inputs), _ptr(front), inputs.shape[0], seed, _ptr(out)), "scatter_batch")
+        if self.lib.prefix == "hrt_":
+            self.lib.check(self.lib.fn("scatter_batch")(self.h, material, _ptr(inputs), _ptr(front), inputs.shape[0], seed, rng_mode, _ptr(out)), "scatter_batch")
+        else:
+            self.lib.check(self.lib.fn("scatter_batch")(self.h, material, _ptr(inputs), _ptr(front), inputs.shape[0], seed, _ptr(out)), "scatter_batch")
         return out
 
     def texture_eval(self, tex: int, uvp: np.ndarray) -> np.ndarray:

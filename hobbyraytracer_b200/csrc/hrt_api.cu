@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <unordered_map>
 #include <string>
@@ -65,6 +66,12 @@ struct BlockCache {
 };
 BlockCache g_blocks;
 
+struct DevBuf {                       // scoped device scratch: freed on every exit path
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 1); }
+};
+
 struct DevUp {
     std::vector<void*>& allocs; std::unordered_map<void*, size_t>& sizes; int device;
     bool failed = false; std::string msg; size_t bytes = 0;
@@ -80,11 +87,17 @@ struct DevUp {
         return d;
     }
     const void* put_copy(const void* p, size_t n) { return put(p, n); }
+    const std::vector<DMesh>* dev_override = nullptr;           // replicas of hrt_render_multi: the device-built meshes copied to their device
+    DMesh dev_mesh(size_t i, const HostShape& sh) { return (dev_override && i < dev_override->size()) ? (*dev_override)[i] : sh.dev; }
 };
 } // namespace
 
 struct hrt_scene {
-    HostScene host;
+    std::shared_ptr<HostScene> host_owner = std::make_shared<HostScene>();   // shared with the per-device replicas of hrt_render_multi
+    HostScene& host = *host_owner;
+    hrt_scene() = default;
+    explicit hrt_scene(const std::shared_ptr<HostScene>& h) : host_owner(h) {}
+    hrt_scene(const hrt_scene&) = delete;
     DScene d{};
     int device = 0, sm_count = 148;
     cudaStream_t stream = nullptr;
@@ -108,6 +121,9 @@ struct hrt_scene {
     double ms_build_gpu = 0; int bvh_fallbacks = 0;             // HRT_BVH_LBVH_GPU: upload + device build time, meshes handed back to the host builder
     std::vector<DMesh> meshes_view;                             // host copy of DScene::meshes (hrt_scene_mesh_array)
     std::vector<std::pair<cudaIpcMemHandle_t, void*>> peers;    // peer films opened through CUDA IPC (closed with the scene)
+    std::vector<hrt_scene*> replicas;                           // hrt_render_multi: this scene on the other devices (same host scene, own uploads)
+    std::vector<DMesh> dev_meshes;                              // device-built meshes (HRT_BVH_LBVH_GPU) as they live on THIS device, by mesh index
+    bool is_replica = false;
 };
 
 namespace {
@@ -268,8 +284,7 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
     cudaEvent_t ev_begin = s->events[EV_PER_CHUNK * CTL_RING], ev_end = s->events[EV_PER_CHUNK * CTL_RING + 1];
 
     const bool wide = s->d.wide && !mega && !v1 && !getenv("HRT_NO_WIDE");     // the pipeline over the 8-wide trees (hrt_wide.cuh)
-    const bool merged = wide && getenv("HRT_WAVE3_MERGED");                   // A/B: camera paths in the phase kernel too
-    WaveCtl init{}; init.total_paths = (mega || v1) ? total : (merged ? wave3_total_claims(j) : wave2_total_claims(j));
+    WaveCtl init{}; init.total_paths = (mega || v1) ? total : wave2_total_claims(j);
     CK(cudaMemcpyAsync(j.ctl, &init, sizeof(init), cudaMemcpyHostToDevice, st));
     CK(cudaEventRecord(ev_begin, st));
     s->stats.paths += total;
@@ -304,7 +319,7 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
             for (int k = 0; k < CHUNK; ++k, ++it) {
                 CK(cudaEventRecord(ev[2 * k], st));
                 if (v1) launch_wave_trace(s->d, j, it, s->sm_count, st, &s->stats.launches);
-                else if (wide) launch_wave3_trace(s->d, j, dc, it, secondary_heavy, merged, s->sm_count, st, &s->stats.launches);
+                else if (wide) launch_wave3_trace(s->d, j, dc, it, secondary_heavy, s->sm_count, st, &s->stats.launches);
                 else launch_wave2_trace(s->d, j, dc, it, secondary_heavy, s->sm_count, st, &s->stats.launches);
                 CK(cudaEventRecord(ev[2 * k + 1], st));
                 if (v1) launch_wave_shade(s->d, j, dc, it, s->sm_count, st, &s->stats.launches);
@@ -370,7 +385,10 @@ void hrt_trim(void)
 void hrt_scene_destroy(hrt_scene* s)
 {
     if (!s) return;
+    for (hrt_scene* r : s->replicas) hrt_scene_destroy(r);
+    s->replicas.clear();
     if (s->host.committed || s->stream) {
+        int cur_dev = 0; cudaGetDevice(&cur_dev);
         cudaSetDevice(s->device);
         cudaDeviceSynchronize();                                   // nothing may still be using what gets parked
         {
@@ -394,6 +412,7 @@ void hrt_scene_destroy(hrt_scene* s)
         for (auto& pr : s->peers) cudaIpcCloseMemHandle(pr.second);
         for (cudaEvent_t e : s->events) cudaEventDestroy(e);
         if (s->stream) cudaStreamDestroy(s->stream);
+        if (s->is_replica) cudaSetDevice(cur_dev);
     }
     delete s;
 }
@@ -515,17 +534,54 @@ int hrt_trace_batch(hrt_scene* s, const float* rays, int64_t n, uint32_t* prim_i
     CK(cudaMemcpyAsync(prim_id, s->tb_prim, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(t, s->tb_t, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, st));
     if (normal || uv || front) {
-        float* d_n = nullptr; float* d_uv = nullptr; uint8_t* d_f = nullptr;
-        if (normal) CK(cudaMalloc(&d_n, sizeof(float) * 3 * (size_t)n));
-        if (uv) CK(cudaMalloc(&d_uv, sizeof(float) * 2 * (size_t)n));
-        if (front) CK(cudaMalloc(&d_f, (size_t)n));
+        DevBuf bn, bu, bf;                                                      // freed on every exit path
+        if (normal) CK(bn.alloc(sizeof(float) * 3 * (size_t)n));
+        if (uv) CK(bu.alloc(sizeof(float) * 2 * (size_t)n));
+        if (front) CK(bf.alloc((size_t)n));
+        float* d_n = (float*)bn.p; float* d_uv = (float*)bu.p; uint8_t* d_f = (uint8_t*)bf.p;
         launch_eval_batch(s->d, s->tb_rays, s->tb_hits, n, d_n, d_uv, d_f, s->sm_count, st, &s->stats.launches);
         if (normal) CK(cudaMemcpyAsync(normal, d_n, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost, st));
         if (uv) CK(cudaMemcpyAsync(uv, d_uv, sizeof(float) * 2 * (size_t)n, cudaMemcpyDeviceToHost, st));
         if (front) CK(cudaMemcpyAsync(front, d_f, (size_t)n, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
-        cudaFree(d_n); cudaFree(d_uv); cudaFree(d_f);
     }
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// ---- parity entries for the shading half of the path: Texture::colourValue and Material::scatter / emitted on batches ----------------
+int hrt_texture_eval(hrt_scene* s, int texture, const float* uvp, int64_t n, float* out_rgb)
+{
+    if (!s || n < 0 || (n > 0 && (!uvp || !out_rgb))) { g_err = "bad argument"; return HRT_ERR_ARG; }
+    if (!s->host.committed) { g_err = "scene not committed"; return HRT_ERR_STATE; }
+    if (texture < 0 || texture >= s->d.n_textures) { g_err = "unknown texture"; return HRT_ERR_ARG; }
+    if (n == 0) return 0;
+    CK(cudaSetDevice(s->device));
+    DevBuf in, out;
+    CK(in.alloc(sizeof(float) * 5 * (size_t)n)); CK(out.alloc(sizeof(float) * 3 * (size_t)n));
+    cudaStream_t st = s->stream;
+    CK(cudaMemcpyAsync(in.p, uvp, sizeof(float) * 5 * (size_t)n, cudaMemcpyHostToDevice, st));
+    launch_texture_eval(s->d, texture, (const float*)in.p, n, (float*)out.p, s->sm_count, st, &s->stats.launches);
+    CK(cudaMemcpyAsync(out_rgb, out.p, sizeof(float) * 3 * (size_t)n, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    return 0;
+}
+int hrt_scatter_batch(hrt_scene* s, int material, const float* in14, const uint8_t* front, int64_t n, uint64_t seed, int rng_mode, float* out10)
+{
+    if (!s || n < 0 || (n > 0 && (!in14 || !front || !out10))) { g_err = "bad argument"; return HRT_ERR_ARG; }
+    if (!s->host.committed) { g_err = "scene not committed"; return HRT_ERR_STATE; }
+    if (material < 0 || material >= s->d.n_materials) { g_err = "unknown material"; return HRT_ERR_ARG; }
+    if (n == 0) return 0;
+    CK(cudaSetDevice(s->device));
+    DevBuf in, fr, out;
+    CK(in.alloc(sizeof(float) * 14 * (size_t)n)); CK(fr.alloc((size_t)n)); CK(out.alloc(sizeof(float) * 10 * (size_t)n));
+    cudaStream_t st = s->stream;
+    CK(cudaMemcpyAsync(in.p, in14, sizeof(float) * 14 * (size_t)n, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(fr.p, front, (size_t)n, cudaMemcpyHostToDevice, st));
+    launch_scatter_batch(s->d, material, (const float*)in.p, (const uint8_t*)fr.p, n, seed, rng_mode, (float*)out.p, s->sm_count, st, &s->stats.launches);
+    CK(cudaMemcpyAsync(out10, out.p, sizeof(float) * 10 * (size_t)n, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
     return 0;
@@ -743,3 +799,120 @@ int hrt_reset_stats(hrt_scene* s)
 }
 
 } // extern "C"
+
+// ---- one process, several GPUs (main.cpp:176 stays ONE synchronous call) -------------------------------------------
+namespace {
+// this scene on another device: the same host scene, its own uploads, streams and work buffers
+int make_replica(hrt_scene* s, int device, hrt_scene** out)
+{
+    hrt_scene* r = new (std::nothrow) hrt_scene(s->host_owner);
+    if (!r) { g_err = "out of memory"; return HRT_ERR_ARG; }
+    r->device = device; r->is_replica = true;
+    auto fail = [&](const std::string& why) { g_err = why; cudaSetDevice(device); free_scene_device(r); if (r->stream) cudaStreamDestroy(r->stream); delete r; cudaSetDevice(s->device); return HRT_ERR_CUDA; };
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&r->sm_count, cudaDevAttrMultiProcessorCount, device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) return fail(std::string("replica set-up: ") + cudaGetErrorString(e));
+    // meshes that were built on the primary's device (HRT_BVH_LBVH_GPU): their arrays cross NVLink, nothing is rebuilt
+    r->dev_meshes.resize(s->host.mesh_shapes.size());
+    for (size_t i = 0; i < s->host.mesh_shapes.size(); ++i) {
+        const HostShape& sh = s->host.shapes[(size_t)s->host.mesh_shapes[i]];
+        if (!sh.has_dev) continue;
+        DMesh m = sh.dev;
+        const void* src[6] = {sh.dev.ref_nodes, sh.dev.tris, sh.dev.attrs, sh.dev.fast_nodes, sh.dev.fast_leaves, sh.dev.wide_nodes};
+        const size_t bytes[6] = {sh.n_ref_nodes * 32, (size_t)sh.n_tri * 48, (size_t)sh.n_tri * 64, sh.n_fast_nodes * 64, sh.n_leaves * 128, sh.dev.wide_nodes ? sh.n_wide_nodes * 96 : 0};
+        void* dst[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+        for (int k = 0; k < 6; ++k) {
+            if (!bytes[k] || !src[k]) continue;
+            e = cudaMalloc(&dst[k], bytes[k]);
+            if (e == cudaSuccess) { r->scene_allocs.push_back(dst[k]); r->scene_bytes += bytes[k]; e = cudaMemcpyPeer(dst[k], device, src[k], s->device, bytes[k]); }
+            if (e != cudaSuccess) return fail(std::string("replica mesh copy: ") + cudaGetErrorString(e));
+        }
+        m.ref_nodes = (const float4*)dst[0]; m.tris = (const float4*)dst[1]; m.attrs = (const float4*)dst[2];
+        m.fast_nodes = (const float4*)dst[3]; m.fast_leaves = (const float4*)dst[4]; m.wide_nodes = (const WNode*)dst[5];
+        r->dev_meshes[i] = m;
+    }
+    DevUp up(r->scene_allocs, r->scene_alloc_bytes, device);
+    up.dev_override = &r->dev_meshes;
+    r->d = make_dscene(s->host, up);
+    r->d.refill_secondary = s->d.refill_secondary;
+    if (up.failed) return fail("replica upload failed: " + up.msg);
+    r->scene_bytes += up.bytes;
+    e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) return fail(std::string("replica upload: ") + cudaGetErrorString(e));
+    cudaSetDevice(s->device);
+    *out = r;
+    return 0;
+}
+} // namespace
+
+extern "C" int hrt_render_multi(hrt_scene* s, const int* devices, int n_devices, const hrt_camera* cam, const hrt_render_params* p, float* out_sum, uint8_t* out_rgb8)
+{
+    int rc = check_render_args(s, cam, p); if (rc < 0) return rc;
+    if (!devices || n_devices < 1 || n_devices > HRT_MAX_PEERS + 1) { g_err = "bad device list"; return HRT_ERR_ARG; }
+    if (devices[0] != s->device) { g_err = "devices[0] must be the device the scene was committed on"; return HRT_ERR_ARG; }
+    if (p->sample_first != 0 || (p->sample_count > 0 && p->sample_count != p->spp)) { g_err = "hrt_render_multi splits all spp samples itself"; return HRT_ERR_ARG; }
+    for (int a = 0; a < n_devices; ++a) for (int b = a + 1; b < n_devices; ++b) if (devices[a] == devices[b]) { g_err = "a device is listed twice"; return HRT_ERR_ARG; }
+    if (n_devices == 1) return hrt_render(s, cam, p, out_sum, out_rgb8);
+    CK(cudaSetDevice(s->device));
+    std::vector<hrt_scene*> part((size_t)n_devices, nullptr);
+    part[0] = s;
+    for (int k = 1; k < n_devices; ++k) {
+        for (hrt_scene* r : s->replicas) if (r->device == devices[k]) part[(size_t)k] = r;
+        if (!part[(size_t)k]) { hrt_scene* r = nullptr; rc = make_replica(s, devices[k], &r); if (rc < 0) return rc; s->replicas.push_back(r); part[(size_t)k] = r; }
+    }
+    const size_t npix = (size_t)p->width * p->height;
+    // every device renders its contiguous share of the sample indices into its own integer film (hrt_render_accumulate_device's contract)
+    std::vector<int> status((size_t)n_devices, 0); std::vector<std::string> errs((size_t)n_devices);
+    auto work = [&](int k) {
+        hrt_scene* r = part[(size_t)k];
+        const int base = p->spp / n_devices, extra = p->spp % n_devices;
+        hrt_render_params q = *p;
+        q.sample_first = k * base + std::min(k, extra); q.sample_count = base + (k < extra ? 1 : 0);
+        int st = 0;
+        if (cudaSetDevice(r->device) != cudaSuccess) st = HRT_ERR_CUDA;
+        if (st == 0) st = ensure_film(r, npix);
+        if (st == 0 && cudaMemsetAsync(r->d_film, 0, sizeof(long long) * FILM_LANES * npix, r->stream) != cudaSuccess) st = HRT_ERR_CUDA;
+        if (st == 0 && q.sample_count > 0) st = render_into(r, cam, &q, r->d_film, r->stream);
+        if (st == 0 && cudaStreamSynchronize(r->stream) != cudaSuccess) st = HRT_ERR_CUDA;
+        status[(size_t)k] = st; if (st < 0) errs[(size_t)k] = g_err.empty() ? "CUDA failure on a worker" : g_err;
+    };
+    std::vector<std::thread> th;
+    for (int k = 1; k < n_devices; ++k) th.emplace_back(work, k);
+    work(0);
+    for (auto& t : th) t.join();
+    for (int k = 0; k < n_devices; ++k) if (status[(size_t)k] < 0) { g_err = "device " + std::to_string(devices[k]) + ": " + errs[(size_t)k]; return status[(size_t)k]; }
+    // reduce + resolve in one kernel on devices[0]: the other films are read in place over NVLink (peer access), or staged when the
+    // devices cannot address each other
+    CK(cudaSetDevice(s->device));
+    const long long* peers[HRT_MAX_PEERS]; std::vector<void*> staged;
+    for (int k = 1; k < n_devices; ++k) {
+        int can = 0; CK(cudaDeviceCanAccessPeer(&can, s->device, devices[k]));
+        if (can) {
+            cudaError_t e = cudaDeviceEnablePeerAccess(devices[k], 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+            if (e != cudaSuccess) can = 0;
+        }
+        if (can) peers[k - 1] = part[(size_t)k]->d_film;
+        else {
+            void* tmp = nullptr; CK(cudaMalloc(&tmp, sizeof(long long) * FILM_LANES * npix)); staged.push_back(tmp);
+            CK(cudaMemcpyPeer(tmp, s->device, part[(size_t)k]->d_film, devices[k], sizeof(long long) * FILM_LANES * npix));
+            peers[k - 1] = (const long long*)tmp;
+        }
+    }
+    cudaStream_t st = s->stream;
+    uint8_t* d_rgb8 = (uint8_t*)(s->d_out + npix * 3);
+    launch_film_resolve_peers(s->d_film, peers, n_devices - 1, (int)npix, p->spp, 0, out_sum ? s->d_out : nullptr, nullptr, out_rgb8 ? d_rgb8 : nullptr, s->sm_count, st, &s->stats.launches);
+    if (out_sum) CK(cudaMemcpyAsync(out_sum, s->d_out, sizeof(float) * npix * 3, cudaMemcpyDeviceToHost, st));
+    if (out_rgb8) CK(cudaMemcpyAsync(out_rgb8, d_rgb8, npix * 3, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    for (void* t : staged) cudaFree(t);
+    CK(cudaGetLastError());
+    for (int k = 1; k < n_devices; ++k) {                                         // one set of counters for the caller
+        hrt_stats& a = s->stats; hrt_stats& b = part[(size_t)k]->stats;
+        a.rays += b.rays; a.paths += b.paths; a.launches += b.launches; a.retraced += b.retraced; a.prim_tests += b.prim_tests;
+        a.ms_trace = std::max(a.ms_trace, b.ms_trace); a.ms_shade = std::max(a.ms_shade, b.ms_shade); a.ms_total = std::max(a.ms_total, b.ms_total);
+        b = hrt_stats{};
+    }
+    return 0;
+}

@@ -15,6 +15,8 @@
 // Compiled with -fmad=false (numerics contract, hrt_math.cuh).
 #include <cuda_runtime.h>
 
+#include <cstdlib>
+
 #include "hrt_kernels.h"
 #include "hrt_shade.cuh"
 #include "hrt_wide.cuh"
@@ -33,7 +35,7 @@ __device__ __forceinline__ RngKey make_key(uint64_t seed, uint32_t index, uint32
 
 // ---- K7 ---------------------------------------------------------------------------------------------------------------
 #ifndef HRT_BATCH_MIN_BLOCKS
-#define HRT_BATCH_MIN_BLOCKS 4
+#define HRT_BATCH_MIN_BLOCKS 5      // 96 registers: ray batch 1355 (4 blocks) / 1493 (5) / 1453 (6) / 1078 (8) Mrays/s on B200 (profiles/README.md r2f)
 #endif
 // Pending rays (pass 1 could not decide: hrt_wide.cuh) are listed here and settled by k_resolve_* afterwards.
 struct PendList { unsigned int* idx; unsigned int* count; };
@@ -128,6 +130,35 @@ __global__ void __launch_bounds__(BLOCK) k_eval_batch(DScene s, const float4* __
         if (normal) { normal[i * 3] = rec.n.x; normal[i * 3 + 1] = rec.n.y; normal[i * 3 + 2] = rec.n.z; }
         if (uv) { uv[i * 2] = rec.u; uv[i * 2 + 1] = rec.v; }
         if (front) front[i] = rec.front ? 1 : 0;
+    }
+}
+
+// ---- Texture::colourValue / Material::scatter + emitted on caller-supplied batches (parity entries, like K7 for hit()) -----------------
+__global__ void __launch_bounds__(BLOCK) k_texture_eval(DScene s, int tex, const float* __restrict__ in, long long n, float* __restrict__ out)
+{
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const V3 c = tex_value(s, tex, in[i * 5], in[i * 5 + 1], v3(in[i * 5 + 2], in[i * 5 + 3], in[i * 5 + 4]));
+        out[i * 3] = c.x; out[i * 3 + 1] = c.y; out[i * 3 + 2] = c.z;
+    }
+}
+// in: r_in.o, r_in.d, rec.p, rec.normal, rec.u, rec.v (14 floats) + frontFace; out: scattered?, attenuation, scattered.dir, emitted (10 floats).
+// Random numbers: the Philox stream of (seed; index i, sample 0), bounce 0 - what a path at its first segment would draw.
+__global__ void __launch_bounds__(BLOCK) k_scatter_batch(DScene s, int material, const float* __restrict__ in, const uint8_t* __restrict__ front, long long n,
+                                                         uint64_t seed, int rng_mode, float* __restrict__ out)
+{
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const float* a = in + i * 14;
+        Ray rin; rin.o = v3(a[0], a[1], a[2]); rin.d = v3(a[3], a[4], a[5]);
+        Rec rec; rec.p = v3(a[6], a[7], a[8]); rec.n = v3(a[9], a[10], a[11]); rec.u = a[12]; rec.v = a[13];
+        rec.front = front[i] != 0; rec.t = 1.0f; rec.mat = material; rec.prim = 0;
+        V3 att = v3(0.0f); Ray sc; sc.o = v3(0.0f); sc.d = v3(0.0f);
+        const RngKey key = make_key(seed, (uint32_t)i, (uint32_t)((unsigned long long)i >> 32), rng_mode);
+        const V3 em = mat_emitted(s, material, rec.u, rec.v, rec.p);
+        const bool ok = mat_scatter(s, material, rin, rec, att, sc, key, 0);
+        float* o = out + i * 10;
+        o[0] = ok ? 1.0f : 0.0f; o[1] = att.x; o[2] = att.y; o[3] = att.z; o[4] = sc.d.x; o[5] = sc.d.y; o[6] = sc.d.z; o[7] = em.x; o[8] = em.y; o[9] = em.z;
     }
 }
 
@@ -457,9 +488,13 @@ __device__ __forceinline__ bool camera_ray_clears_scene(const DScene& s, const R
     return tn > tf || tf < fminf(t_min, 0.0f);
 }
 
-template <int MINB, bool LENS>
+// WIDE: the walks of a step of the warp (32 entries, or the 32 camera rays of one sample of the claim) go through the 8-wide trees
+// together, in phases (hrt_wide.cuh, no refill: the claim structure stays); used on scenes with large meshes, where the
+// two-child walk is a chain of ~50 dependent fetches per ray.
+template <int MINB, bool LENS, bool WIDE>
 __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j, DCamera cam, int q, int skip_secondary)
 {
+    __shared__ int stack_mem[WIDE ? WIDE_STACK * BLOCK : 1];
     WaveCtl* c = j.ctl;
     const unsigned int n_sec = c->n_front[q];
     const unsigned long long total_claims = c->total_paths;
@@ -517,11 +552,20 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j
             ++c_sl; --c_left;
         }
         Hit h; h.t = 0.0f; h.prim = HRT_MISS; h.obj = -1; h.flags = 0;
-        if (active && !(primary && s.has_bounds && camera_ray_clears_scene(s, r, j.t_min))) {
-            RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + (int)((st >> 8) & 0x7fffffu)), j.rng_mode);
-            h = s.fast ? trace_fast<false>(s, r, j.t_min, hrt_inf(), key, st & 0xffu, nullptr) : trace_ref(s, r, j.t_min, hrt_inf(), key, st & 0xffu);
-            if (h.flags & (HIT_RESOLVED | HIT_FALLBACK)) atomicAdd((h.flags & HIT_FALLBACK) ? &c->fallbacks : &c->resolved, 1ull);
-        }
+        const bool walk = active && !(primary && s.has_bounds && camera_ray_clears_scene(s, r, j.t_min));
+        const RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + (int)((st >> 8) & 0x7fffffu)), j.rng_mode);
+        if (WIDE) {
+            WideSmemStack<BLOCK> stk; stk.base = stack_mem + threadIdx.x; stk.sp = 0;
+            WideLane L; L.live = false; L.b.bad = 0;
+            bool began = false;
+            if (walk) began = wide_begin(L, s, r, j.t_min, hrt_inf(), h);
+            while (wide_round(L, s, stk, key, st & 0xffu)) { }
+            if (walk && (began || L.b.bad)) {
+                h = wide_result(L);
+                if (h.flags & HIT_PENDING) h = wide_resolve(s, r, j.t_min, hrt_inf(), key, st & 0xffu, h);
+            }
+        } else if (walk) h = s.fast ? trace_fast<false>(s, r, j.t_min, hrt_inf(), key, st & 0xffu, nullptr) : trace_ref(s, r, j.t_min, hrt_inf(), key, st & 0xffu);
+        if (h.flags & (HIT_RESOLVED | HIT_FALLBACK)) atomicAdd((h.flags & HIT_FALLBACK) ? &c->fallbacks : &c->resolved, 1ull);
         if (!primary) {
             if (active) j.hits[sec_i] = h;
             sec_i += stride;
@@ -601,7 +645,7 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave2_shade(DScene s, WaveJob j
 // Persistent warps, per-lane refill from the queue's hand-out counter, phases (hrt_wide.cuh); records go to hits[entry], rays
 // that need pass 2 to WaveJob::pend (k_wave3_resolve).  Runs before k_wave2_trace, which is told to skip these entries.
 #ifndef HRT_WSEC_MIN_BLOCKS
-#define HRT_WSEC_MIN_BLOCKS 4
+#define HRT_WSEC_MIN_BLOCKS 5      // teapot_scene 1501 (4 blocks) / 1611 (5) / 1504 (6) / 1292 (8) Mrays/s (r2f)
 #endif
 __global__ void __launch_bounds__(BLOCK, HRT_WSEC_MIN_BLOCKS) k_wide_secondary(DScene s, WaveJob j, int q)
 {
@@ -648,188 +692,7 @@ __global__ void __launch_bounds__(BLOCK, HRT_WSEC_MIN_BLOCKS) k_wide_secondary(D
     }
 }
 
-// ---- the wavefront over the 8-wide trees (scenes with DScene::wide; hrt_wide.cuh) -----------------------------------------------
-// ONE persistent kernel per iteration replaces k_wave2_secondary + k_wave2_trace: every lane walks its own ray, and a lane
-// whose walk ended takes the next piece of work as soon as fewer than HRT_WIDE_REFILL lanes of its warp are walking —
-//   first a secondary entry of queue q (global hand-out counter; its record goes to hits[entry]),
-//   then the next sample of ITS pixel of the warp's claim (an 8x4 tile x CLAIM3_SPP samples): the camera ray is generated
-//   (K1), settled on the spot when it cannot reach the scene bounds, walked otherwise;  miss -> background + film sum in
-//   shared memory (K4/K5), hit -> appended behind the secondary entries (warp ballot + one atomic, K3) for the shade pass.
-// The lanes of a warp are therefore at different samples of their pixels; a claim ends when every lane has used its samples.
-// Walks advance in phases (hrt_wide.cuh): no instruction of the node / leaf / entry code runs for a handful of lanes while
-// the rest of the warp waits, which is what the lock-step k_wave2_trace did on every scene whose camera rays mostly miss
-// (shiny_teapot: 15 % of the lanes walked while 85 % waited).  Rays that need pass 2 get a pending record and are listed in
-// WaveJob::pend; k_wave3_resolve settles them before the shade pass.  Integer film: same bits as every other pipeline.
-#ifndef HRT_CLAIM3_SPP
-#define HRT_CLAIM3_SPP 8
-#endif
-#ifndef HRT_WAVE3_MIN_BLOCKS
-#define HRT_WAVE3_MIN_BLOCKS 4
-#endif
-constexpr int CLAIM3_SPP = HRT_CLAIM3_SPP;
-constexpr int CLAIM3 = 32 * CLAIM3_SPP;
-
-__host__ __device__ inline unsigned int wave3_sblocks(const WaveJob& j) { return ((unsigned int)j.s_count + CLAIM3_SPP - 1u) / CLAIM3_SPP; }
-
-// per-thread film sums of the current claim in shared memory: lanes q[0..2] fixed point, [3] flag fields (hrt_shade.cuh)
-struct SmemAcc {
-    long long* base;        // &mem[threadIdx.x]; entry k at base[k * BLOCK]
-    __device__ __forceinline__ void clear() { base[0] = 0; base[BLOCK] = 0; base[2 * BLOCK] = 0; base[3 * BLOCK] = 0; }
-    __device__ __forceinline__ void add(V3 c)
-    {
-        const float v[3] = {c.x, c.y, c.z};
-        unsigned long long flags = 0;
-#pragma unroll
-        for (int ch = 0; ch < 3; ++ch) {
-            long long q; unsigned long long flag;
-            film_quantize(v[ch], ch, q, flag);
-            if (q != 0) base[ch * BLOCK] += q;
-            flags |= flag;
-        }
-        if (flags) base[3 * BLOCK] |= (long long)flags;
-    }
-    __device__ __forceinline__ void flush(long long* film, int pix)
-    {
-        long long* px = film + (size_t)pix * FILM_LANES;
-#pragma unroll
-        for (int ch = 0; ch < 3; ++ch) { const long long q = base[ch * BLOCK]; if (q != 0) atomicAdd((unsigned long long*)(px + ch), (unsigned long long)q); }
-        const long long f = base[3 * BLOCK];
-        if (f) atomicOr((unsigned long long*)(px + 3), (unsigned long long)f);
-        clear();
-    }
-};
-
-template <bool LENS>
-__global__ void __launch_bounds__(BLOCK, HRT_WAVE3_MIN_BLOCKS) k_wave3_trace(DScene s, WaveJob j, DCamera cam, int q)
-{
-    __shared__ int stack_mem[WIDE_STACK * BLOCK];
-    __shared__ long long acc_mem[4 * BLOCK];
-    WideSmemStack<BLOCK> st; st.base = stack_mem + threadIdx.x; st.sp = 0;
-    SmemAcc acc; acc.base = acc_mem + threadIdx.x; acc.clear();
-    WaveCtl* c = j.ctl;
-    const unsigned int n_sec = c->n_front[q];
-    const unsigned long long total_claims = c->total_paths;
-    if (blockIdx.x == 0 && threadIdx.x == 0) { c->rays += n_sec; c->n_front[q ^ 1] = 0; }   // nobody reads these in this kernel
-    const unsigned int lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
-    const unsigned int warps_total = gridDim.x * (BLOCK / 32);
-    const unsigned int room = j.capacity - n_sec;                                 // slots left for camera-path hits
-    const unsigned int margin = warps_total * (unsigned int)CLAIM3;               // what the other warps may still append after a check
-    const unsigned int n_units = wave2_units(j);
-    float4* __restrict__ rays = j.rays[q];
-    PendList pend; pend.idx = j.pend; pend.count = &c->pend_count;
-
-    WideLane L; L.live = false;
-    int kind = 0;                       // what this lane's ray is: 0 none, 1 secondary entry, 2 camera path
-    unsigned int e_idx = 0, r_st = 0; int r_pix = 0;        // the ray's queue entry (secondary) / pixel and packed state
-    int c_pix = -1, c_sl = 0, c_left = 0;                   // the warp's claim: this lane's pixel, its next sample, samples left
-    bool sec_done = n_sec == 0, cam_done = false;           // warp-uniform: nothing more to fetch from that source
-    for (;;) {
-        int walking = __popc(__ballot_sync(0xffffffffu, L.live));
-        if (walking < ((sec_done && cam_done) ? 1 : HRT_WIDE_REFILL)) {
-            // ---- retire the walks that ended
-            const bool fin = kind != 0 && !L.live;
-            Hit h; h.t = 0.0f; h.prim = HRT_MISS; h.obj = -1; h.flags = 0;
-            if (fin) h = wide_result(L);
-            if (fin && kind == 1) {
-                j.hits[e_idx] = h;
-                if (h.flags & HIT_PENDING) pend_push(pend, e_idx);
-                kind = 0;
-            }
-            const bool keep = fin && kind == 2 && (h.prim != HRT_MISS || (h.flags & HIT_PENDING));
-            if (fin && kind == 2 && !keep) {                                        // main.cpp:47-59: the path ends on the background
-                const Ray wr = L.r;
-                const V3 bg = background_colour(s, wr);
-                if (r_pix == c_pix) acc.add(bg); else film_add(j.film, r_pix, bg);   // (a ray of the previous claim)
-                kind = 0;
-            }
-            const unsigned int m_keep = __ballot_sync(0xffffffffu, keep);
-            if (m_keep) {
-                unsigned int e0 = 0;
-                if (lane == 0) e0 = atomicAdd(&c->n_prim[q], (unsigned int)__popc(m_keep));
-                e0 = __shfl_sync(0xffffffffu, e0, 0);
-                if (keep) {
-                    const unsigned int e = n_sec + e0 + (unsigned int)__popc(m_keep & below);
-                    rays[2 * (size_t)e] = make_float4(L.r.o.x, L.r.o.y, L.r.o.z, __int_as_float(r_pix));
-                    rays[2 * (size_t)e + 1] = make_float4(L.r.d.x, L.r.d.y, L.r.d.z, __uint_as_float(r_st));
-                    j.hits[e] = h;
-                    if (h.flags & HIT_PENDING) pend_push(pend, e);
-                    kind = 0;
-                }
-            }
-            // ---- fetch: secondary entries first, then camera paths, until enough lanes walk or nothing can be fetched
-            for (;;) {
-                if (!sec_done) {
-                    const unsigned int m = __ballot_sync(0xffffffffu, kind == 0);
-                    if (m) {
-                        unsigned int base = 0;
-                        if (lane == (unsigned int)(__ffs(m) - 1)) base = atomicAdd(&c->sec_next[q], (unsigned int)__popc(m));
-                        base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-                        const unsigned int my = base + (unsigned int)__popc(m & below);
-                        if (kind == 0 && my < n_sec) {
-                            const float4 a = rays[2 * (size_t)my], b = rays[2 * (size_t)my + 1];
-                            Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
-                            r_pix = __float_as_int(a.w); r_st = __float_as_uint(b.w); e_idx = my; kind = 1;
-                            Hit early; st.sp = 0;
-                            if (!wide_begin(L, s, r, j.t_min, hrt_inf(), early)) { L.b.t = early.t; L.b.prim = early.prim; L.b.obj = early.obj; }
-                        }
-                        if (base + (unsigned int)__popc(m) >= n_sec) sec_done = true;
-                    }
-                }
-                if (!cam_done || __any_sync(0xffffffffu, c_left > 0)) {
-                    if (!__any_sync(0xffffffffu, c_left > 0)) {                         // the claim is used up: the next one
-                        if (c_pix >= 0) acc.flush(j.film, c_pix);
-                        c_pix = -1;
-                        unsigned long long k0 = 0;
-                        if (lane == 0 && ld_relaxed(&c->n_prim[q]) + margin <= room && ld_relaxed(&c->next_path) < total_claims)
-                            k0 = atomicAdd(&c->next_path, 1ull) + 1ull;
-                        k0 = __shfl_sync(0xffffffffu, k0, 0);
-                        if (k0 == 0 || k0 - 1ull >= total_claims) cam_done = true;
-                        else {
-                            const unsigned int k = (unsigned int)(k0 - 1ull);
-                            const unsigned int sb = k / n_units, unit = k - sb * n_units;    // claims of one sample block sweep the film
-                            c_sl = (int)sb * CLAIM3_SPP;
-                            c_left = j.s_count - c_sl < CLAIM3_SPP ? j.s_count - c_sl : CLAIM3_SPP;
-                            if (j.tiles_x > 0) {
-                                const int x = (int)(unit % (unsigned int)j.tiles_x) * 8 + (int)(lane & 7u);
-                                const int y = (int)(unit / (unsigned int)j.tiles_x) * 4 + (int)(lane >> 3);
-                                c_pix = y * j.width + x;
-                            } else {
-                                const unsigned int pp = unit * 32u + lane;
-                                c_pix = pp < (unsigned int)j.npix ? (int)pp : -1;
-                            }
-                            if (c_pix < 0) c_left = 0;
-                        }
-                    }
-                    if (kind == 0 && c_left > 0) {                                   // this lane's next sample (main.cpp:115-123)
-                        const int x = c_pix % j.width, y = c_pix / j.width;
-                        const RngKey key = make_key(j.seed, (uint32_t)c_pix, (uint32_t)(j.s_first + c_sl), j.rng_mode);
-                        const Ray r = primary_ray_xy<LENS>(cam, j.width, j.height, x, j.height - y, key);
-                        r_pix = c_pix; r_st = pack_state(c_sl, 0, false);
-                        ++c_sl; --c_left;
-                        if (s.has_bounds && camera_ray_clears_scene(s, r, j.t_min)) acc.add(background_colour(s, r));
-                        else {
-                            Hit early; st.sp = 0; kind = 2;
-                            if (!wide_begin(L, s, r, j.t_min, hrt_inf(), early)) { L.r = r; L.b.t = early.t; L.b.prim = early.prim; L.b.obj = early.obj; }
-                        }
-                    }
-                }
-                walking = __popc(__ballot_sync(0xffffffffu, L.live));
-                if (walking >= HRT_WIDE_REFILL) break;
-                const bool more_cam = !cam_done || __any_sync(0xffffffffu, c_left > 0);
-                // camera work can only be fetched by idle lanes that still have samples, or by a new claim once every lane is out of samples
-                const bool cam_possible = more_cam && (__any_sync(0xffffffffu, kind == 0 && c_left > 0) || !__any_sync(0xffffffffu, c_left > 0));
-                if (!(!sec_done && __any_sync(0xffffffffu, kind == 0)) && !cam_possible) break;
-            }
-        }
-        const RngKey key = make_key(j.seed, (uint32_t)r_pix, (uint32_t)(j.s_first + (int)((r_st >> 8) & 0x7fffffu)), j.rng_mode);
-        if (!wide_round(L, s, st, key, r_st & 0xffu)) {
-            if (sec_done && cam_done && !__any_sync(0xffffffffu, kind != 0)) break;
-        }
-    }
-    if (c_pix >= 0) acc.flush(j.film, c_pix);
-}
-
-// pass 2 of the entries k_wave3_trace left pending (ties, badly conditioned triangles, NaNs: hrt_trace.cuh), before the shade pass
+// pass 2 of the entries k_wide_secondary left pending (ties, badly conditioned triangles, NaNs: hrt_trace.cuh), before the shade pass
 __global__ void __launch_bounds__(BLOCK) k_wave3_resolve(DScene s, WaveJob j, int q)
 {
     WaveCtl* c = j.ctl;
@@ -887,9 +750,18 @@ void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit*
     cudaMemsetAsync(d_counter, 0, sizeof(unsigned long long), st);
     cudaMemsetAsync(d_pend_count, 0, sizeof(unsigned int), st);
     PendList pend; pend.idx = d_pend_idx; pend.count = d_pend_count;
-    if (!s.wide) { k_trace_batch_plain<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed); *launches += 1; return; }
+    if (!s.wide || getenv("HRT_NO_WIDE")) { k_trace_batch_plain<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed); *launches += 1; return; }
     k_trace_batch<<<grid_for(n, sm_count, HRT_BATCH_MIN_BLOCKS), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed, d_counter, pend);
     k_resolve_batch<<<sm_count * 2, BLOCK, 0, st>>>(s, d_rays, d_hits, seed, pend); *launches += 2;
+}
+void launch_texture_eval(const DScene& s, int tex, const float* d_in, long long n, float* d_out, int sm_count, cudaStream_t st, uint64_t* launches)
+{
+    k_texture_eval<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, tex, d_in, n, d_out); *launches += 1;
+}
+void launch_scatter_batch(const DScene& s, int material, const float* d_in, const uint8_t* d_front, long long n, uint64_t seed, int rng_mode, float* d_out,
+                          int sm_count, cudaStream_t st, uint64_t* launches)
+{
+    k_scatter_batch<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, material, d_in, d_front, n, seed, rng_mode, d_out); *launches += 1;
 }
 void launch_split_hits(const Hit* d_hits, long long n, uint32_t* d_prim, float* d_t, int sm_count, cudaStream_t st, uint64_t* launches)
 {
@@ -934,41 +806,41 @@ void launch_wave2_trace(const DScene& s, const WaveJob& j, const DCamera& cam, i
     if (refill) { k_wave2_secondary<<<sm_count * HRT_DYN_MIN_BLOCKS, BLOCK, 0, st>>>(s, j, it & 1); *launches += 1; }
     const bool lens = cam.lens_radius > 0.0f;             // HRT_RENDER_DEFOCUS: the instantiation with the lens sampling compiled in
     if (secondary_heavy) {
-        if (lens) k_wave2_trace<8, true><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
-        else k_wave2_trace<8, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
+        if (lens) k_wave2_trace<8, true, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
+        else k_wave2_trace<8, false, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
     } else {
-        if (lens) k_wave2_trace<4, true><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
-        else k_wave2_trace<4, false><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
+        if (lens) k_wave2_trace<4, true, false><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
+        else k_wave2_trace<4, false, false><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);
     }
     *launches += 1;
 }
-unsigned long long wave3_total_claims(const WaveJob& j) { return (unsigned long long)wave2_units(j) * (unsigned long long)wave3_sblocks(j); }
-void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, bool secondary_heavy, bool merged, int sm_count, cudaStream_t st, uint64_t* launches)
+#ifndef HRT_WTRACE_MIN_BLOCKS
+#define HRT_WTRACE_MIN_BLOCKS 4
+#endif
+void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, bool secondary_heavy, int sm_count, cudaStream_t st, uint64_t* launches)
 {
-    if (merged) {                                                                   // A/B: secondary entries and camera paths in one phase kernel
-        long long cap = (long long)j.capacity / (4ll * CLAIM3 * (BLOCK / 32));      // keeps the append margin below 1/4 of the queue
-        long long want = (long long)sm_count * HRT_WAVE3_MIN_BLOCKS;                // one resident wave: the warps loop until the work is gone
-        if (cap < 1) cap = 1;
-        const int blocks = (int)(want < cap ? want : cap);
-        if (cam.lens_radius > 0.0f) k_wave3_trace<true><<<blocks, BLOCK, 0, st>>>(s, j, cam, it & 1);
-        else k_wave3_trace<false><<<blocks, BLOCK, 0, st>>>(s, j, cam, it & 1);
-        *launches += 1;
+    // Camera paths: the lock-step fused-primary kernel (most of them are settled by the scene-bounds test and the rest is coherent); on
+    // scenes with large meshes its walks go through the wide trees in phases (WIDE), elsewhere through the two-child trees.
+    // Secondary rays: the phase kernel with per-lane refill where walks are long and uneven - scenes with meshes whose rays are mostly
+    // secondary (teapot_scene 1253 -> 1611 Mrays/s) or whose meshes are large (big_mesh); elsewhere k_wave2_trace's own lock-step
+    // pass is as good or better (B200 A/B r2f: shiny_teapot 8874 vs 8658, scattered_balls 5300 vs 3276, cornell_smoke 4070 vs 3626)
+    const int wsec = (s.refill_secondary && (secondary_heavy || s.big_mesh)) ? 1 : 0;
+    if (wsec) { k_wide_secondary<<<sm_count * HRT_WSEC_MIN_BLOCKS, BLOCK, 0, st>>>(s, j, it & 1); *launches += 1; }
+    const bool lens = cam.lens_radius > 0.0f;
+    const int q = it & 1;
+    if (s.big_mesh) {
+        const int blocks = wave2_trace_blocks(j.capacity, sm_count, HRT_WTRACE_MIN_BLOCKS);
+        if (lens) k_wave2_trace<HRT_WTRACE_MIN_BLOCKS, true, true><<<blocks, BLOCK, 0, st>>>(s, j, cam, q, wsec);
+        else k_wave2_trace<HRT_WTRACE_MIN_BLOCKS, false, true><<<blocks, BLOCK, 0, st>>>(s, j, cam, q, wsec);
+    } else if (secondary_heavy) {
+        if (lens) k_wave2_trace<8, true, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, q, wsec);
+        else k_wave2_trace<8, false, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, q, wsec);
     } else {
-        // secondary rays: phase kernel over the wide trees; camera paths: the lock-step fused-primary kernel (most of them are settled by
-        // the scene-bounds test and the rest is coherent, which the lock-step walk handles well)
-        k_wide_secondary<<<sm_count * HRT_WSEC_MIN_BLOCKS, BLOCK, 0, st>>>(s, j, it & 1);
-        const bool lens = cam.lens_radius > 0.0f;
-        if (secondary_heavy) {
-            if (lens) k_wave2_trace<8, true><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, 1);
-            else k_wave2_trace<8, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, 1);
-        } else {
-            if (lens) k_wave2_trace<4, true><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, 1);
-            else k_wave2_trace<4, false><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, it & 1, 1);
-        }
-        *launches += 2;
+        if (lens) k_wave2_trace<4, true, false><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, q, wsec);
+        else k_wave2_trace<4, false, false><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, q, wsec);
     }
-    k_wave3_resolve<<<sm_count * 2, BLOCK, 0, st>>>(s, j, it & 1);
-    *launches += 1;
+    k_wave3_resolve<<<sm_count * 2, BLOCK, 0, st>>>(s, j, q);
+    *launches += 2;
 }
 void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches)
 {

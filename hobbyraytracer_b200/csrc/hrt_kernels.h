@@ -54,6 +54,9 @@ struct WaveJob {
 // d_pend_idx (n entries) / d_pend_count (one word): scratch for the rays that need pass 2 (hrt_wide.cuh)
 void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed, unsigned long long* d_counter,
                         unsigned int* d_pend_idx, unsigned int* d_pend_count, int sm_count, cudaStream_t st, uint64_t* launches);
+void launch_texture_eval(const DScene& s, int tex, const float* d_in, long long n, float* d_out, int sm_count, cudaStream_t st, uint64_t* launches);
+void launch_scatter_batch(const DScene& s, int material, const float* d_in, const uint8_t* d_front, long long n, uint64_t seed, int rng_mode, float* d_out,
+                          int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_split_hits(const Hit* d_hits, long long n, uint32_t* d_prim, float* d_t, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_eval_batch(const DScene& s, const float4* d_rays, const Hit* d_hits, long long n, float* d_normal, float* d_uv, uint8_t* d_front,
                        int sm_count, cudaStream_t st, uint64_t* launches);
@@ -66,10 +69,9 @@ void launch_wave_shade(const DScene& s, const WaveJob& j, const DCamera& cam, in
 // + shade2(queue it&1 -> survivors to queue (it+1)&1); no init pass, the control block starts zeroed with total_paths set
 unsigned long long wave2_total_claims(const WaveJob& j);   // value of WaveCtl::total_paths for this pipeline (it hands out claims, not paths)
 void launch_wave2_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, bool secondary_heavy, int sm_count, cudaStream_t st, uint64_t* launches);
-// the same pipeline over the 8-wide trees (scenes with DScene::wide): ONE persistent kernel walks the secondary entries and
-// the camera paths in phases with per-lane refill (hrt_wide.cuh), a small second kernel settles the pending entries
-unsigned long long wave3_total_claims(const WaveJob& j);
-void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, bool secondary_heavy, bool merged, int sm_count, cudaStream_t st, uint64_t* launches);
+// the same pipeline on scenes with the 8-wide trees (DScene::wide): secondary entries by the phase kernel with per-lane refill where
+// that pays (hrt_wide.cuh), camera paths by the fused-primary kernel, a small third kernel settles the pending entries
+void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, bool secondary_heavy, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches);
 // one thread per path, whole rayColour loop (validation of the wavefront pipeline); same film
 void launch_render_mega(const DScene& s, const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches);

@@ -103,6 +103,7 @@ struct DScene {
     int n_textures;
     int background;
     int fast;                   // 0: reference visiting order everywhere; 1: SAH BVHs + reference-order re-trace of ambiguous rays
+    int big_mesh;               // 1: some mesh has >= 2^17 triangles (its trees leave L1: the wide walk pays for every ray kind)
     int refill_secondary;       // 1: secondary rays are traced by the per-lane-refill pass (scenes with meshes: long, uneven walks)
     float tlas_cull_scale;      // lower bound of (reported t) / (world t * |d|) over RotateQuat objects; 0 if none
     int has_bounds;             // 1: bounds_lo/hi enclose every world-list entry (camera rays that pass outside are misses)

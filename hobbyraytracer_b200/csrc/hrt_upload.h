@@ -18,7 +18,7 @@ DScene make_dscene(HostScene& s, Up& up)
     for (size_t i = 0; i < s.mesh_shapes.size(); ++i) {
         HostShape& sh = s.shapes[(size_t)s.mesh_shapes[i]];
         DMesh m{};
-        if (sh.has_dev) { m = sh.dev; m.prim_base = (uint32_t)sh.prim_base; m.material = sh.material; meshes[i] = m; continue; }
+        if (sh.has_dev) { m = up.dev_mesh(i, sh); m.prim_base = (uint32_t)sh.prim_base; m.material = sh.material; meshes[i] = m; continue; }   // built on the device: its arrays as they live on the consumer's device
         m.ref_nodes = (const float4*)up.put(sh.ref.nodes.data(), sh.ref.nodes.size() * sizeof(float4));
         m.tris = (const float4*)up.put(sh.tris4.data(), sh.tris4.size() * sizeof(float4));
         m.attrs = (const float4*)up.put(sh.attrs4.data(), sh.attrs4.size() * sizeof(float4));
@@ -61,6 +61,8 @@ DScene make_dscene(HostScene& s, Up& up)
     for (const DMesh& m : meshes) if (m.ref_root >= 0 && m.wide_root >= 0 && m.wide_nodes == nullptr) d.wide = 0;
     for (size_t i = 0; i < s.mesh_shapes.size(); ++i) if (!s.shapes[(size_t)s.mesh_shapes[i]].wide.ok) d.wide = 0;
     d.refill_secondary = (fast && !meshes.empty()) ? 1 : 0;
+    d.big_mesh = 0;
+    for (const DMesh& m : meshes) if (m.n_tri >= (int64_t(1) << 17)) d.big_mesh = 1;
     d.tlas_cull_scale = s.tlas_cull_scale;
     d.has_bounds = (fast && s.has_bounds) ? 1 : 0;
     for (int a = 0; a < 3; ++a) { d.bounds_lo[a] = s.bounds_lo[a]; d.bounds_hi[a] = s.bounds_hi[a]; }

@@ -282,42 +282,50 @@ template <class St> HRT_HD void wide_leaf_step(WideLane& L, const DScene& s, St&
 // ---- world-list entry: a mesh is entered (local ray, marker on the stack), anything else is tested on the spot
 template <class St> HRT_HD void wide_object_step(WideLane& L, const DScene& s, St& st, const RngKey& key, uint32_t bounce)
 {
-    const int i = ~L.cur;
-    const DObject& ob = s.objects[i];
-    if (ob.kind == SHAPE_MESH && !ob.medium) {
-        const DMesh& m = s.meshes[ob.mesh];
-        if (m.ref_root >= 0) {
-            Ray lr = L.r; V3 id = L.rid; bool ok = true;
-            if (ob.xf_count > 0) {
-                lr = to_local(s, ob, L.r);
-                id = v3(1.0f / lr.d.x, 1.0f / lr.d.y, 1.0f / lr.d.z);
-                ok = recip_ok(id) && hrt_finite(lr.o.x) && hrt_finite(lr.o.y) && hrt_finite(lr.o.z);
+    // a lane often holds several entries in a row (the children of one top-level node that the ray's box test let through): up to four
+    // per call, so that a Cornell-box ray does not spend a round of the warp per wall (r2g profile of teapot_scene)
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1                                                                // (unrolled, the kernel outgrows the instruction cache: r2h profile)
+#endif
+    for (int rep = 0; rep < 4; ++rep) {
+        const int i = ~L.cur;
+        const DObject& ob = s.objects[i];
+        if (ob.kind == SHAPE_MESH && !ob.medium) {
+            const DMesh& m = s.meshes[ob.mesh];
+            if (m.ref_root >= 0) {
+                Ray lr = L.r; V3 id = L.rid; bool ok = true;
+                if (ob.xf_count > 0) {
+                    lr = to_local(s, ob, L.r);
+                    id = v3(1.0f / lr.d.x, 1.0f / lr.d.y, 1.0f / lr.d.z);
+                    ok = recip_ok(id) && hrt_finite(lr.o.x) && hrt_finite(lr.o.y) && hrt_finite(lr.o.z);
+                }
+                const int kz = tri_kz(lr.o);
+                if (!ok) L.b.bad = 1;
+                else if (!shear_ok(lr, kz)) L.b.shear = 1;                      // pass 2 collects every hit along this ray
+                else if (!st.push(WALK_MARK)) L.b.bad = 1;
+                else {
+                    L.q = wide_ray(lr.o, lr.d, id);
+                    L.nodes = m.wide_nodes; L.leaves = m.fast_leaves; L.prim_base = m.prim_base; L.obj = i;
+                    L.ld = lr.d; L.tq = tri_ray<3>(lr, kz);
+                    wide_set_bound(L);
+                    L.cur = m.wide_root;
+                    return;
+                }
             }
-            const int kz = tri_kz(lr.o);
-            if (!ok) L.b.bad = 1;
-            else if (!shear_ok(lr, kz)) L.b.shear = 1;                          // pass 2 collects every hit along this ray
-            else if (!st.push(WALK_MARK)) L.b.bad = 1;
+        } else {
+            float t = 0.0f; uint32_t prim = ob.prim_base; bool hit;
+            const float bound = cull_bound(L.b);
+            if (!ob.medium && ob.xf_count == 0 && ob.kind == SHAPE_SPHERE) hit = sphere_t(ob.f, L.r, L.t_min, bound, t);    // the common entries in line
+            else if (!ob.medium && ob.xf_count == 0 && ob.kind == SHAPE_RECT) { float a, b; hit = rect_t(ob.axis, ob.f[0], ob.f[1], ob.f[2], ob.f[3], ob.f[4], L.r, L.t_min, bound, t, a, b); }
             else {
-                L.q = wide_ray(lr.o, lr.d, id);
-                L.nodes = m.wide_nodes; L.leaves = m.fast_leaves; L.prim_base = m.prim_base; L.obj = i;
-                L.ld = lr.d; L.tq = tri_ray<3>(lr, kz);
-                wide_set_bound(L);
-                L.cur = m.wide_root;
-                return;
+                const Ray wr = L.r;                                             // a copy: hit_object_ref is out of line
+                hit = hit_object_ref(s, i, wr, L.t_min, bound, t, prim, key, bounce);
             }
+            if (hit) { consider(L.b, t, t, prim, i); wide_set_bound(L); }
         }
-    } else {
-        float t = 0.0f; uint32_t prim = ob.prim_base; bool hit;
-        const float bound = cull_bound(L.b);
-        if (!ob.medium && ob.xf_count == 0 && ob.kind == SHAPE_SPHERE) hit = sphere_t(ob.f, L.r, L.t_min, bound, t);        // the common entries in line
-        else if (!ob.medium && ob.xf_count == 0 && ob.kind == SHAPE_RECT) { float a, b; hit = rect_t(ob.axis, ob.f[0], ob.f[1], ob.f[2], ob.f[3], ob.f[4], L.r, L.t_min, bound, t, a, b); }
-        else {
-            const Ray wr = L.r;                                                 // a copy: hit_object_ref is out of line
-            hit = hit_object_ref(s, i, wr, L.t_min, bound, t, prim, key, bounce);
-        }
-        if (hit) { consider(L.b, t, t, prim, i); wide_set_bound(L); }
+        wide_pop(L, s, st);
+        if (!(L.live && L.cur < 0 && L.obj < 0)) return;
     }
-    wide_pop(L, s, st);
 }
 
 // what pass 1 found, as a hit record: final, or pending (the caller queues the ray for trace_resolve)

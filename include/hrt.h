@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define HRT_ABI_VERSION 5
+#define HRT_ABI_VERSION 6
 
 /* ---- error codes --------------------------------------------------------------------------- */
 #define HRT_OK            0
@@ -216,6 +216,16 @@ int hrt_trace_batch(hrt_scene* s, const float* rays, int64_t n, uint32_t* prim_i
 int hrt_trace_batch_device(hrt_scene* s, const void* d_rays, int64_t n, void* d_prim_id, void* d_t,
                            uint64_t rng_seed, void* stream);
 
+/* The shading half of the path on caller-supplied batches (parity entries, like hrt_trace_batch for hit()):
+ * hrt_texture_eval: Texture::colourValue(u, v, p) of texture `texture` (texture.h:3-7, texture.cpp:17-97); uvp: n x 5 floats
+ *   (u, v, p.xyz), out_rgb: n x 3.
+ * hrt_scatter_batch: Material::emitted + Material::scatter of material `material` (material.h:60-242, material.cpp:18-28) on n hit
+ *   records; in14: n x 14 floats (r_in.origin, r_in.dir, rec.p, rec.normal, rec.u, rec.v), front: n bytes (rec.frontFace); out10:
+ *   n x 10 floats (scattered ? 1 : 0, attenuation rgb, scattered.dir, emitted rgb).  Record i draws from the Philox stream of
+ *   (seed; index i, sample 0) at bounce 0, rng_mode as in hrt_render_params. */
+int hrt_texture_eval(hrt_scene* s, int texture, const float* uvp, int64_t n, float* out_rgb);
+int hrt_scatter_batch(hrt_scene* s, int material, const float* in14, const uint8_t* front, int64_t n, uint64_t seed, int rng_mode, float* out10);
+
 /* render(): main.cpp:81-140.  out_sum: width*height*3 floats receiving the per-pixel *sum* of the rendered
  * samples (NULL to skip); out_rgb8: width*height*3 bytes = Film::tonemap + writeColour of sum/spp
  * (film.cpp:25-52), row 0 = top row as in the reference's pixel buffer (NULL to skip). */
@@ -236,6 +246,16 @@ int hrt_render_progressive(hrt_scene* s, const hrt_camera* cam, const hrt_render
                            int slice_spp, hrt_progress_fn on_slice, void* user, float* out_sum, uint8_t* out_rgb8);
 /* The checkpoint file on its own (tooling): samples held by a checkpoint, or HRT_ERR_IO.                                 */
 int hrt_checkpoint_samples(const char* checkpoint_path, int* width, int* height, int* spp);
+
+/* render() on several GPUs of one process: main.cpp:176 stays ONE synchronous call.  `devices` lists n_devices distinct CUDA
+ * device ordinals, devices[0] being the one the scene was committed on.  The committed scene is replicated once per extra device
+ * (uploads of the same host arrays; device-built meshes are copied over NVLink) and kept for later calls; one host thread per
+ * device renders a contiguous share of the p->spp sample indices into that device's integer film, and devices[0] sums the films
+ * in place over peer memory and resolves them in one kernel (no collective, no extra process).  The image is bit-identical to
+ * hrt_render's for any number of devices (integer film, Philox keyed by the global sample index).  p->sample_first / sample_count
+ * must select the whole image. */
+int hrt_render_multi(hrt_scene* s, const int* devices, int n_devices, const hrt_camera* cam, const hrt_render_params* p,
+                     float* out_sum, uint8_t* out_rgb8);
 
 /* Device variants for multi-GPU use.  The FILM is a device buffer of hrt_film_bytes(width, height) bytes:
  * per pixel four int64 lanes — the r, g, b sample sums in fixed point (2^-26 units; every sample rounded to

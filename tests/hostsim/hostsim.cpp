@@ -27,6 +27,7 @@ thread_local std::string g_err;
 struct HostUp {
     std::deque<std::vector<char>> keep;
     const void* put(const void* p, size_t n) { return n ? p : nullptr; }
+    DMesh dev_mesh(size_t, const HostShape& sh) { return sh.dev; }
     const void* put_copy(const void* p, size_t n) { if (!n) return nullptr; keep.emplace_back((const char*)p, (const char*)p + n); return keep.back().data(); }
 };
 template <class F> void parallel_for(int64_t n, int64_t chunk, F&& fn)

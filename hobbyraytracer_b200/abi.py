@@ -52,7 +52,7 @@ class RenderParams(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("paths", C.c_uint64), ("launches", C.c_uint64), ("ms_trace", C.c_double),
                 ("ms_shade", C.c_double), ("ms_other", C.c_double), ("ms_total", C.c_double),
-                ("node_tests", C.c_uint64), ("prim_tests", C.c_uint64), ("retraced", C.c_uint64),
+                ("film_clamped", C.c_uint64), ("prim_tests", C.c_uint64), ("retraced", C.c_uint64),
                 ("scene_bytes", C.c_uint64), ("ms_build", C.c_double),
                 ("h2d_bytes", C.c_uint64), ("ms_build_upload", C.c_double)]
 

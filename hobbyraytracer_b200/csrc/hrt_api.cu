@@ -342,7 +342,7 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
     float ms = 0; CK(cudaEventElapsedTime(&ms, ev_begin, ev_end));
     s->stats.ms_total += ms;
     s->stats.rays += fin.rays + ((mega || v1) ? 0ull : total);       // fused-primary: the control block counts the secondary rays only
-    s->stats.retraced += fin.resolved; s->stats.prim_tests += fin.fallbacks;
+    s->stats.retraced += fin.resolved; s->stats.prim_tests += fin.fallbacks; s->stats.film_clamped += fin.clamped;
     if (fin.fallbacks && getenv("HRT_DEBUG_FALLBACK"))
         for (unsigned long long k = 0; k < fin.fallbacks && k < 16; ++k) {
             const float* g = fin.dbg[k]; unsigned int st; memcpy(&st, &g[7], 4); int pix; memcpy(&pix, &g[3], 4);
@@ -910,7 +910,7 @@ extern "C" int hrt_render_multi(hrt_scene* s, const int* devices, int n_devices,
     CK(cudaGetLastError());
     for (int k = 1; k < n_devices; ++k) {                                         // one set of counters for the caller
         hrt_stats& a = s->stats; hrt_stats& b = part[(size_t)k]->stats;
-        a.rays += b.rays; a.paths += b.paths; a.launches += b.launches; a.retraced += b.retraced; a.prim_tests += b.prim_tests;
+        a.rays += b.rays; a.paths += b.paths; a.launches += b.launches; a.retraced += b.retraced; a.prim_tests += b.prim_tests; a.film_clamped += b.film_clamped;
         a.ms_trace = std::max(a.ms_trace, b.ms_trace); a.ms_shade = std::max(a.ms_shade, b.ms_shade); a.ms_total = std::max(a.ms_total, b.ms_total);
         b = hrt_stats{};
     }

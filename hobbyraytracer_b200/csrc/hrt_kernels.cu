@@ -164,13 +164,19 @@ __global__ void __launch_bounds__(BLOCK) k_scatter_batch(DScene s, int material,
 
 // ---- film ---------------------------------------------------------------------------------------------------------------
 // quantisation / flag fields / reconstruction live in hrt_shade.cuh (shared with the CPU simulation harness)
-__device__ __forceinline__ void film_add(long long* film, int pix, V3 c)
+// a finite sample beyond the film's +-2^FILM_MAG_BITS range is clamped (hrt_shade.cuh) - and counted, so that callers can tell
+__device__ __forceinline__ void count_clamped(unsigned long long* counter, float v)
+{
+    if (fabsf(v) > (float)(1 << FILM_MAG_BITS) && fabsf(v) <= 3.402823466e+38f) atomicAdd(counter, 1ull);
+}
+__device__ __forceinline__ void film_add(long long* film, int pix, V3 c, unsigned long long* clamped)
 {
     long long* px = film + (size_t)pix * FILM_LANES;
     const float v[3] = {c.x, c.y, c.z};
 #pragma unroll
     for (int ch = 0; ch < 3; ++ch) {
         if (v[ch] == 0.0f) continue;
+        count_clamped(clamped, v[ch]);
         long long q; unsigned long long flag;
         film_quantize(v[ch], ch, q, flag);
         if (flag) atomicOr((unsigned long long*)(px + 3), flag);
@@ -340,7 +346,7 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave_shade(DScene s, WaveJob j,
             go = go && (int)bounce + 1 < j.max_depth;                           // MAX_DEPTH reached: the partial sum stands (main.cpp:43,78)
             if (go) st = pack_state(sl, (int)bounce + 1, has_result);
             else {
-                if (has_result) film_add(j.film, pix, result);                  // px += rayColour(...)  main.cpp:123
+                if (has_result) film_add(j.film, pix, result, &c->clamped);                  // px += rayColour(...)  main.cpp:123
                 fresh = true;
             }
         }
@@ -399,11 +405,12 @@ __host__ __device__ inline unsigned int wave2_units(const WaveJob& j) { return j
 __host__ __device__ inline unsigned int wave2_sblocks(const WaveJob& j) { return ((unsigned int)j.s_count + CLAIM_SPP - 1u) / CLAIM_SPP; }
 
 struct FilmAcc { long long q[3]; unsigned long long flags; };
-__device__ __forceinline__ void acc_add(FilmAcc& a, V3 c)
+__device__ __forceinline__ void acc_add(FilmAcc& a, V3 c, unsigned long long* clamped)
 {
     const float v[3] = {c.x, c.y, c.z};
 #pragma unroll
     for (int ch = 0; ch < 3; ++ch) {
+        count_clamped(clamped, v[ch]);
         long long q; unsigned long long flag;
         film_quantize(v[ch], ch, q, flag);
         a.q[ch] += q; a.flags |= flag;
@@ -572,7 +579,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j
             continue;
         }
         const bool hit = active && h.prim != HRT_MISS;
-        if (active && !hit) acc_add(acc, background_colour(s, r));                  // main.cpp:47-59: the path ends on the background
+        if (active && !hit) acc_add(acc, background_colour(s, r), &c->clamped);                  // main.cpp:47-59: the path ends on the background
         const unsigned int m_hit = __ballot_sync(0xffffffffu, hit);
         if (m_hit) {
             unsigned int e0 = 0;
@@ -618,7 +625,7 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave2_shade(DScene s, WaveJob j
             if (rad.x != 0.0f || rad.y != 0.0f || rad.z != 0.0f) { result = result + rad; has_result = true; }
             go = go && (int)bounce + 1 < j.max_depth;                               // MAX_DEPTH reached: the partial sum stands (main.cpp:43,78)
             if (go) st = pack_state(sl, (int)bounce + 1, has_result);
-            else if (has_result) film_add(j.film, pix, result);                     // px += rayColour(...)  main.cpp:123
+            else if (has_result) film_add(j.film, pix, result, &c->clamped);                     // px += rayColour(...)  main.cpp:123
         }
         const unsigned int m_go = __ballot_sync(0xffffffffu, go);
         if (lane == 0) w_go[warp] = (unsigned int)__popc(m_go);
@@ -728,7 +735,7 @@ __global__ void __launch_bounds__(BLOCK) k_render_mega(DScene s, WaveJob j, DCam
             if (rad.x != 0.0f || rad.y != 0.0f || rad.z != 0.0f) { result = result + rad; has_result = true; }
             if (!go) break;
         }
-        if (has_result) film_add(j.film, pix, result);
+        if (has_result) film_add(j.film, pix, result, &j.ctl->clamped);
     }
     if (rays) atomicAdd(&j.ctl->rays, rays);
 }

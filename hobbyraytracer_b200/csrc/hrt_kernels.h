@@ -20,6 +20,7 @@ struct WaveCtl {
     unsigned long long rays;            // closest-hit queries issued
     unsigned long long resolved;        // rays answered by pass 2 + replay (hrt_trace.cuh)
     unsigned long long fallbacks;       // rays answered by trace_ref
+    unsigned long long clamped;         // finite sample channels beyond the film's +-2^21 range (clamped, hrt_shade.cuh)
     unsigned int sec_next[2];           // fused-primary pipeline: hand-out counter of the secondary entries of queue q (per-lane refill)
     unsigned int n_prim[2];             // fused-primary pipeline: camera-path hits appended behind the n_front[q] secondary entries of queue q
     unsigned int pend_count;            // wide pipeline: entries of the current queue whose hit record is pending (WaveJob::pend), reset by the shade pass

@@ -282,12 +282,9 @@ template <class St> HRT_HD void wide_leaf_step(WideLane& L, const DScene& s, St&
 // ---- world-list entry: a mesh is entered (local ray, marker on the stack), anything else is tested on the spot
 template <class St> HRT_HD void wide_object_step(WideLane& L, const DScene& s, St& st, const RngKey& key, uint32_t bounce)
 {
-    // a lane often holds several entries in a row (the children of one top-level node that the ray's box test let through): up to four
-    // per call, so that a Cornell-box ray does not spend a round of the warp per wall (r2g profile of teapot_scene)
-#if defined(__CUDA_ARCH__)
-#pragma unroll 1                                                                // (unrolled, the kernel outgrows the instruction cache: r2h profile)
-#endif
-    for (int rep = 0; rep < 4; ++rep) {
+    // (one entry per call: taking a lane's next entries in the same call - a Cornell-box ray holds three in a row - was slower,
+    // teapot_scene 1612 -> 1496 Mrays/s, and unrolled it outgrew the instruction cache: 931, profiles/README.md r2h / r2i)
+    {
         const int i = ~L.cur;
         const DObject& ob = s.objects[i];
         if (ob.kind == SHAPE_MESH && !ob.medium) {
@@ -324,7 +321,6 @@ template <class St> HRT_HD void wide_object_step(WideLane& L, const DScene& s, S
             if (hit) { consider(L.b, t, t, prim, i); wide_set_bound(L); }
         }
         wide_pop(L, s, st);
-        if (!(L.live && L.cur < 0 && L.obj < 0)) return;
     }
 }
 

@@ -130,7 +130,8 @@ typedef struct hrt_stats {
     double   ms_shade;        /* device time in the shading / regeneration kernel                    */
     double   ms_other;        /* raygen, film, resets                                                */
     double   ms_total;        /* device time of the whole call                                       */
-    uint64_t node_tests;      /* reserved                                                            */
+    uint64_t film_clamped;    /* finite sample channels beyond the film's +-2^21 range (clamped before the integer add;
+                                 a reference float sum would not clamp): 0 on every BASELINE config (tested)              */
     uint64_t prim_tests;      /* rays answered by the last-resort reference-order walk (NaN t, zero direction components) */
     uint64_t retraced;        /* rays whose answer depended on the visiting order and was settled by replaying the
                                  reference's sequential process over the collected candidates (HRT_BVH_SAH only) */

@@ -147,43 +147,113 @@ def test_teapot_scene_rays(orc, hrt, cache_dir):
 # ---- renders ---------------------------------------------------------------------------------------------------------------
 def render_case(name, cache_dir):
     if name == "teapot_scene":
-        sd, cam, _ = scenes.teapot_scene(cache_dir, n=24, env_w=128, env_h=64); return sd, cam, 72, 72, 96
+        sd, cam, _ = scenes.teapot_scene(cache_dir, n=24, env_w=128, env_h=64); return sd, cam, 128, 128, 128
     if name == "shiny_teapot":
-        sd, cam, _ = scenes.shiny_teapot_scene(cache_dir, n=24, env_w=256, env_h=128); return sd, cam, 96, 54, 64
+        sd, cam, _ = scenes.shiny_teapot_scene(cache_dir, n=24, env_w=256, env_h=128); return sd, cam, 192, 112, 128
     if name == "shiny_teapot_glass":
-        sd, cam, _ = scenes.shiny_teapot_scene(cache_dir, n=24, env_w=256, env_h=128, rough_dielectric=True); return sd, cam, 96, 54, 64
+        sd, cam, _ = scenes.shiny_teapot_scene(cache_dir, n=24, env_w=256, env_h=128, rough_dielectric=True); return sd, cam, 192, 112, 128
     if name == "scattered_balls":
-        sd, cam, _ = scenes.scattered_balls_scene(seed=42, grid=4); return sd, cam, 96, 64, 64
+        sd, cam, _ = scenes.scattered_balls_scene(seed=42, grid=4); return sd, cam, 192, 128, 64
     if name == "cornell_smoke":
-        sd, cam, _ = scenes.cornell_smoke_scene(glass_sphere=True); return sd, cam, 64, 64, 256
+        sd, cam, _ = scenes.cornell_smoke_scene(glass_sphere=True); return sd, cam, 96, 96, 256
     raise KeyError(name)
+
+
+def block_sums(img, ok, bs=16):
+    """Sums over bs x bs pixel blocks (all channels) of the pixels flagged ok -> (sums, element counts), one entry per block."""
+    h, w, _ = img.shape
+    hb, wb = h // bs, w // bs
+    v = np.where(ok[..., None], img, 0.0)[:hb * bs, :wb * bs].astype(np.float64).reshape(hb, bs, wb, bs, 3).sum(axis=(1, 3, 4))
+    n = ok[:hb * bs, :wb * bs].reshape(hb, bs, wb, bs).sum(axis=(1, 3)) * 3
+    return v.reshape(-1), n.reshape(-1)
+
+
+def block_gate(a, b, g, ok, bs=16):
+    """16 x 16 block means of g against the mean of the two oracle renders a, b.  The noise of ONE render's block mean is measured in
+    the block itself, from the per-pixel sample variance over the three renders (heavy tails: a firefly that only one render caught
+    widens that block's limit, a bias of g over a whole block adds delta^2 / 3 per pixel to it and stays visible).  Returns the largest
+    |g_b - (a_b + b_b) / 2| in units of its limit max(1 % of the block mean, 7 sigma of that difference: oracle against oracle reaches 4.5 - 5.8)."""
+    sa, n = block_sums(a, ok, bs); sb, _ = block_sums(b, ok, bs); sg, _ = block_sums(g, ok, bs)
+    m = (a.astype(np.float64) + b + g) / 3.0
+    sd2, _ = block_sums(((a - m) ** 2 + (b - m) ** 2 + (g - m) ** 2) / 2.0, ok, bs)
+    full = n == n.max()
+    n = np.maximum(n, 1)
+    mid = 0.5 * (sa + sb) / n
+    sigma = np.sqrt(sd2) / n
+    limit = np.maximum(0.01 * np.abs(mid), 7.0 * sigma * np.sqrt(1.5))
+    return float((np.abs(sg / n - mid)[full] / np.maximum(limit[full], 1e-12)).max()), int(full.sum())
 
 
 @pytest.mark.parametrize("name", ["teapot_scene", "shiny_teapot", "shiny_teapot_glass", "scattered_balls", "cornell_smoke"])
 def test_render_matches_oracle_within_noise(orc, hrt, cache_dir, name):
-    """Noise-floor-calibrated image gate: RMSE(gpu, A) <= 1.25 RMSE(A, B) for two oracle seeds A, B at
-    equal spp; global mean within 3 sigma of the A/B spread (>= 1 %); 8x8 block means likewise."""
+    """Noise-floor-calibrated image gate, GPU against two oracle renders A, B of other seeds at equal spp:
+      * RMSE(gpu, A) <= 1.25 RMSE(A, B);
+      * 16 x 16 block means: |gpu - (A + B) / 2| <= 1 % of the block mean, or 7 sigma of that block's own noise, measured from the
+        per-pixel differences A - B inside it (a biased lobe that keeps the global mean shows here);
+      * global mean within 0.5 %, or 3 |mean A - mean B|;
+      * rays per camera sample within 1 % of the oracle's (the path-length statistics: scatter verdicts, absorption, misses);
+      * no sample was clamped by the film;
+    the three image gates on radiance clipped at the 99.9th percentile of A (the reference is a brute-force path tracer: a handful of
+    fireflies carries most of the variance of a Cornell-type frame)."""
     sd, cam, w, h, spp = render_case(name, cache_dir)
     c = scenes.camera_for(cam, w, h)
     o = sd.build(orc, 0, 3)
-    A, _ = o.render_f32(c, w, h, spp, seed=101); B, _ = o.render_f32(c, w, h, spp, seed=202)
+    A, rays_a = o.render_f32(c, w, h, spp, seed=101); B, rays_b = o.render_f32(c, w, h, spp, seed=202)
     A /= spp; B /= spp
     ok = np.isfinite(A).all(-1) & np.isfinite(B).all(-1)
+    lim = float(np.percentile(A[ok], 99.9))
     for mode in MODES:
         g = sd.build(hrt, mode, 3)
         S, rgb = g.render(c, w, h, spp, seed=7)
+        st = g.stats()
         G = S / spp
         okg = ok & np.isfinite(G).all(-1)
         assert okg.mean() > 0.99
+        a, b, gg = np.minimum(A, lim), np.minimum(B, lim), np.minimum(G, lim)
         rmse = lambda x, y: float(np.sqrt(np.mean((x[okg] - y[okg]) ** 2)))
-        floor = rmse(A, B)
-        assert rmse(G, A) <= 1.25 * floor + 1e-6, (name, mode, rmse(G, A), floor)
-        ma, mb, mg = A[okg].mean(), B[okg].mean(), G[okg].mean()
-        assert abs(mg - 0.5 * (ma + mb)) <= 3 * abs(ma - mb) + 0.02 * ma, (name, mode, ma, mb, mg)
+        floor = rmse(a, b)
+        assert rmse(gg, a) <= 1.25 * floor + 1e-6, (name, mode, rmse(gg, a), floor)
+        ma, mb, mg = a[okg].mean(), b[okg].mean(), gg[okg].mean()
+        assert abs(mg - 0.5 * (ma + mb)) <= max(0.005 * ma, 3 * abs(ma - mb)), (name, mode, ma, mb, mg)
+        worst, n_blocks = block_gate(a, b, gg, okg)
+        assert worst <= 1.0 and n_blocks >= 30, (name, mode, worst, n_blocks)
+        assert abs(st.rays / st.paths - 0.5 * (rays_a + rays_b) / (w * h * spp)) <= 0.01 * rays_a / (w * h * spp), (name, mode, st.rays / st.paths, rays_a / (w * h * spp))
+        assert st.film_clamped == 0
         # 8-bit film: the GPU's tonemap of its own sums equals the oracle's film code on the same sums, bit for bit
         ref8 = np.empty((h, w, 3), np.uint8)
         orc.check(orc.fn("film_resolve")(np.ascontiguousarray(S).ctypes.data, w, h, spp, ref8.ctypes.data))
         assert np.array_equal(ref8, rgb)
+
+
+def eight_bit_case(name, cache_dir):
+    """-> scene, camera, oracle spp: the spp at which the oracle's own 8-bit noise is ~1.9 / 255 (measured: RMSE(A, B) at 256 spp is
+    3.2 on the shiny teapot, 2.0 on the balls, 3.7 on the big mesh: profiles/README.md r2j)"""
+    if name == "shiny_teapot":
+        sd, cam, _ = scenes.shiny_teapot_scene(cache_dir, n=24, env_w=256, env_h=128); return sd, cam, 384
+    if name == "scattered_balls":
+        sd, cam, _ = scenes.scattered_balls_scene(seed=42, grid=4); return sd, cam, 256
+    sd, cam, _ = scenes.big_mesh_scene(cache_dir, quads=120, env_w=256, env_h=128); return sd, cam, 512
+
+
+@pytest.mark.parametrize("name", ["shiny_teapot", "scattered_balls", "big_mesh"])
+def test_eight_bit_image_against_oracle(orc, hrt, cache_dir, name):
+    """SURVEY.md §8d, env / sky-lit configs (C2, C3, C5 style) at 480 x 270: the final 8-bit image (ACES + gamma) within 2 / 255 RMSE
+    of the CPU oracle's.  Spp on each side: the oracle at 256-512 (see eight_bit_case), the GPU at 4096 - its own noise then adds
+    under 10 % to the oracle's, which is what the bound has to absorb."""
+    sd, cam, spp_cpu = eight_bit_case(name, cache_dir)
+    w, h, spp_gpu = 480, 270, 4096
+    c = scenes.camera_for(cam, w, h)
+    A, rays_a = sd.build(orc, 0, 3).render_f32(c, w, h, spp_cpu, seed=31)
+    a8 = np.empty((h, w, 3), np.uint8)
+    orc.check(orc.fn("film_resolve")(np.ascontiguousarray(A).ctypes.data, w, h, spp_cpu, a8.ctypes.data))
+    g = sd.build(hrt, abi.BVH_SAH, 3)
+    _, g8 = g.render(c, w, h, spp_gpu, seed=7)
+    st = g.stats()
+    rmse8 = float(np.sqrt(np.mean((a8.astype(np.float64) - g8.astype(np.float64)) ** 2)))
+    assert rmse8 <= 2.0, (name, rmse8)
+    assert abs(a8.astype(np.float64).mean() - g8.astype(np.float64).mean()) <= 0.5, "mean 8-bit level"
+    assert abs(st.rays / st.paths - rays_a / (w * h * spp_cpu)) <= 0.01 * rays_a / (w * h * spp_cpu)
+    assert st.film_clamped == 0
 
 
 def test_wavefront_equals_megakernel_and_sample_split(hrt, cache_dir):

@@ -136,7 +136,12 @@ class Lib:
         self._sig("checkpoint_samples", i, [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)], required=False)
         self._sig("render_accumulate_device", i, [_vp, C.POINTER(Camera), C.POINTER(RenderParams), _vp, _vp], required=False)
         self._sig("film_resolve_device", i, [_vp, _vp, i, i, i, _vp, _vp, _vp, _vp], required=False)
-        self._sig("film_bytes", i, [i, i], required=False)
+        self._sig("film_bytes", i64, [i, i], required=False)
+        self._sig("peer_alloc", _vp, [i64], required=False)
+        self._sig("peer_free", None, [_vp], required=False)
+        self._sig("peer_handle", i, [_vp, _vp], required=False)
+        self._sig("peer_open", _vp, [_vp, _vp], required=False)
+        self._sig("film_resolve_slice", i, [_vp, _vp, i, i, i, i, i, i, _vp, _vp, _vp, _vp], required=False)
         self._sig("film_create", _vp, [i, i], required=False)
         self._sig("film_destroy", None, [_vp], required=False)
         self._sig("film_zero", i, [_vp, i, i, _vp], required=False)

@@ -252,6 +252,9 @@ int check_render_args(hrt_scene* s, const hrt_camera* cam, const hrt_render_para
     if (p->width < 2 || p->height < 2 || p->spp < 1) { g_err = "width/height must be >= 2 and spp >= 1"; return HRT_ERR_ARG; }
     if ((long long)p->width * p->height > 0x3fffffffll) { g_err = "film too large"; return HRT_ERR_ARG; }
     if (p->sample_first < 0) { g_err = "negative sample_first"; return HRT_ERR_ARG; }
+    // the wavefront packs (has_result, local sample index, bounce) into one word: 1 + 23 + 8 bits (hrt_kernels.cu, pack_state)
+    if (p->max_depth > 255) { g_err = "max_depth above 255"; return HRT_ERR_ARG; }
+    if ((p->sample_count > 0 ? p->sample_count : p->spp) > 0x7fffff) { g_err = "more than 2^23 - 1 samples in one call (render in slices: sample_first / sample_count)"; return HRT_ERR_ARG; }
     return 0;
 }
 
@@ -387,6 +390,7 @@ void hrt_scene_destroy(hrt_scene* s)
     if (!s) return;
     for (hrt_scene* r : s->replicas) hrt_scene_destroy(r);
     s->replicas.clear();
+    if (!s->peers.empty()) { cudaSetDevice(s->device); for (auto& pr : s->peers) cudaIpcCloseMemHandle(pr.second); s->peers.clear(); }
     if (s->host.committed || s->stream) {
         int cur_dev = 0; cudaGetDevice(&cur_dev);
         cudaSetDevice(s->device);
@@ -409,7 +413,6 @@ void hrt_scene_destroy(hrt_scene* s)
         free_job(s); free_tb(s); free_scene_device(s);
         cudaFree(s->d_film); cudaFree(s->d_out); cudaFree(s->d_counter);
         if (s->h_ctl) cudaFreeHost(s->h_ctl);
-        for (auto& pr : s->peers) cudaIpcCloseMemHandle(pr.second);
         for (cudaEvent_t e : s->events) cudaEventDestroy(e);
         if (s->stream) cudaStreamDestroy(s->stream);
         if (s->is_replica) cudaSetDevice(cur_dev);
@@ -481,7 +484,8 @@ int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed)
     s->scene_bytes = up.bytes + dev_bytes; s->h2d_bytes += up.bytes;
     s->meshes_view.resize(s->host.mesh_shapes.size());
     if (!s->meshes_view.empty()) CK(cudaMemcpy(s->meshes_view.data(), s->d.meshes, s->meshes_view.size() * sizeof(DMesh), cudaMemcpyDeviceToHost));
-    CK(cudaDeviceSynchronize());
+    CK(cudaStreamSynchronize(s->stream));                          // (uploads are synchronous copies, device builds run on s->stream: no device-wide
+                                                                   //  wait, so a host thread can commit the next scene while another one renders)
     for (HostShape& sh : s->host.shapes) sh.release_borrowed();   // HRT_MESH_BORROW ends here
     s->host.committed = true;
     return 0;
@@ -587,10 +591,10 @@ int hrt_scatter_batch(hrt_scene* s, int material, const float* in14, const uint8
     return 0;
 }
 
-int hrt_film_bytes(int width, int height)
+int64_t hrt_film_bytes(int width, int height)
 {
-    if (width < 1 || height < 1 || (long long)width * height > 0x3fffffffll / 8) { g_err = "bad film size"; return HRT_ERR_ARG; }
-    return (int)((long long)width * height * FILM_LANES * (long long)sizeof(long long));
+    if (width < 1 || height < 1 || (long long)width * height > 0x3fffffffll) { g_err = "bad film size"; return HRT_ERR_ARG; }
+    return (int64_t)width * height * FILM_LANES * (int64_t)sizeof(long long);
 }
 
 int hrt_render_accumulate_device(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, void* d_film, void* stream)
@@ -598,6 +602,7 @@ int hrt_render_accumulate_device(hrt_scene* s, const hrt_camera* cam, const hrt_
     int rc = check_render_args(s, cam, p); if (rc < 0) return rc;
     if (!d_film) { g_err = "d_film is NULL"; return HRT_ERR_ARG; }
     CK(cudaSetDevice(s->device));
+    if (!stream) CK(cudaStreamSynchronize(cudaStreamLegacy));      // NULL = the scene's own (non-blocking) stream: what the caller queued on the default stream first
     return render_into(s, cam, p, (long long*)d_film, stream ? (cudaStream_t)stream : s->stream);
 }
 
@@ -606,6 +611,7 @@ int hrt_film_resolve_device(hrt_scene* s, const void* d_film, int width, int hei
     if (!s || !d_film || width < 1 || height < 1 || spp < 1) { g_err = "bad argument"; return HRT_ERR_ARG; }
     CK(cudaSetDevice(s->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+    if (!stream) CK(cudaStreamSynchronize(cudaStreamLegacy));
     launch_film_resolve((const long long*)d_film, width * height, spp, (float*)d_sum, (float*)d_mean, (uint8_t*)d_rgb8, s->sm_count, st, &s->stats.launches);
     CK(cudaGetLastError());
     return 0;
@@ -737,7 +743,7 @@ int hrt_render_progressive(hrt_scene* s, const hrt_camera* cam, const hrt_render
 
 void* hrt_film_create(int width, int height)
 {
-    const int bytes = hrt_film_bytes(width, height);
+    const int64_t bytes = hrt_film_bytes(width, height);
     if (bytes < 0) return nullptr;
     void* p = nullptr;
     cudaError_t e = cudaSetDevice(g_device);
@@ -749,9 +755,10 @@ void* hrt_film_create(int width, int height)
 void hrt_film_destroy(void* d_film) { if (d_film) cudaFree(d_film); }
 int hrt_film_zero(void* d_film, int width, int height, void* stream)
 {
-    const int bytes = hrt_film_bytes(width, height);
+    const int64_t bytes = hrt_film_bytes(width, height);
     if (!d_film || bytes < 0) { g_err = "bad argument"; return HRT_ERR_ARG; }
-    CK(cudaMemsetAsync(d_film, 0, (size_t)bytes, (cudaStream_t)stream));
+    if (stream) CK(cudaMemsetAsync(d_film, 0, (size_t)bytes, (cudaStream_t)stream));
+    else CK(cudaMemset(d_film, 0, (size_t)bytes));                  // NULL: done when the call returns, so ordered before anything queued afterwards
     return 0;
 }
 int hrt_film_ipc_handle(void* d_film, void* out_handle)
@@ -780,7 +787,49 @@ int hrt_film_resolve_peers(hrt_scene* s, void* d_film, const void* peer_handles,
         ptrs[k] = (const long long*)p;
     }
     cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+    if (!stream) CK(cudaStreamSynchronize(cudaStreamLegacy));
     launch_film_resolve_peers((long long*)d_film, ptrs, n_peers, width * height, spp, write_back, (float*)d_sum, (float*)d_mean, (uint8_t*)d_rgb8,
+                              s->sm_count, st, &s->stats.launches);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+// ---- peer-mappable buffers and the reduction spread over the ranks ------------------------------------------------------------------
+void* hrt_peer_alloc(int64_t bytes)
+{
+    if (bytes <= 0) { g_err = "bad size"; return nullptr; }
+    void* p = nullptr;
+    cudaError_t e = cudaSetDevice(g_device);
+    if (e == cudaSuccess) e = cudaMalloc(&p, (size_t)bytes);
+    if (e == cudaSuccess) e = cudaMemset(p, 0, (size_t)bytes);
+    if (e != cudaSuccess) { g_err = std::string("hrt_peer_alloc: ") + cudaGetErrorString(e); if (p) cudaFree(p); return nullptr; }
+    return p;
+}
+void hrt_peer_free(void* p) { if (p) cudaFree(p); }
+int hrt_peer_handle(void* p, void* out_handle) { return hrt_film_ipc_handle(p, out_handle); }
+void* hrt_peer_open(hrt_scene* s, const void* handle)
+{
+    if (!s || !handle) { g_err = "NULL argument"; return nullptr; }
+    cudaIpcMemHandle_t h; memcpy(&h, handle, sizeof(h));
+    for (auto& pr : s->peers) if (memcmp(&pr.first, &h, sizeof(h)) == 0) return pr.second;
+    void* p = nullptr;
+    cudaError_t e = cudaSetDevice(s->device);
+    if (e == cudaSuccess) e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { g_err = std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e); cudaGetLastError(); return nullptr; }
+    s->peers.emplace_back(h, p);
+    return p;
+}
+int hrt_film_resolve_slice(hrt_scene* s, const void* const* films, int n_films, int width, int height, int spp, int pix_first, int pix_count,
+                           void* d_sum, void* d_mean, void* d_rgb8, void* stream)
+{
+    if (!s || !films || n_films < 1 || n_films > 16 || width < 1 || height < 1 || spp < 1 || pix_first < 0 || pix_count < 0 ||
+        (long long)pix_first + pix_count > (long long)width * height) { g_err = "bad argument"; return HRT_ERR_ARG; }
+    for (int k = 0; k < n_films; ++k) if (!films[k]) { g_err = "NULL film"; return HRT_ERR_ARG; }
+    if (pix_count == 0) return 0;
+    CK(cudaSetDevice(s->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+    if (!stream) CK(cudaStreamSynchronize(cudaStreamLegacy));
+    launch_film_resolve_slice((const long long* const*)films, n_films, pix_first, pix_count, spp, (float*)d_sum, (float*)d_mean, (uint8_t*)d_rgb8,
                               s->sm_count, st, &s->stats.launches);
     CK(cudaGetLastError());
     return 0;

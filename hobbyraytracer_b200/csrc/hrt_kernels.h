@@ -81,6 +81,9 @@ void launch_render_mega(const DScene& s, const WaveJob& j, const DCamera& cam, i
 // the same over the local film + up to 15 peer films mapped through CUDA IPC (NVLink loads inside the kernel)
 void launch_film_resolve_peers(long long* d_film, const long long* const* peers, int n_peers, int npix, int spp, int write_back,
                                 float* d_sum, float* d_mean, uint8_t* d_rgb8, int sm_count, cudaStream_t st, uint64_t* launches);
+// the reduction spread over the ranks: pixels [pix_first, pix_first + pix_count) of up to 16 films (own + mapped peers) -> outputs (may be peer memory)
+void launch_film_resolve_slice(const long long* const* films, int n_films, int pix_first, int pix_count, int spp,
+                               float* d_sum, float* d_mean, uint8_t* d_rgb8, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_film_resolve(const long long* d_film, int npix, int spp, float* d_sum, float* d_mean, uint8_t* d_rgb8, int sm_count, cudaStream_t st, uint64_t* launches);
 
 } // namespace hrt

@@ -266,8 +266,9 @@ int hrt_render_multi(hrt_scene* s, const int* devices, int n_devices, const hrt_
  * any GPU count.  The caller zeroes the film; hrt_render_accumulate_device adds sample indices
  * [sample_first, sample_first + sample_count) of every pixel; hrt_film_resolve_device turns a (reduced) film
  * into float sums / float means (sum / spp, main.cpp:126) / the 8-bit image (film.cpp:25-52), any of which
- * may be NULL. */
-int hrt_film_bytes(int width, int height);
+ * may be NULL.  `stream` is a cudaStream_t; NULL selects the scene's own (non-blocking) stream, and the call then first waits for
+ * whatever the caller queued on the legacy default stream (hrt_film_zero with NULL is complete when it returns). */
+int64_t hrt_film_bytes(int width, int height);
 int hrt_render_accumulate_device(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
                                  void* d_film, void* stream);
 int hrt_film_resolve_device(hrt_scene* s, const void* d_film, int width, int height, int spp,
@@ -287,6 +288,22 @@ int   hrt_film_zero(void* d_film, int width, int height, void* stream);
 int   hrt_film_ipc_handle(void* d_film, void* out_handle);
 int   hrt_film_resolve_peers(hrt_scene* s, void* d_film, const void* peer_handles, int n_peers, int width, int height, int spp,
                              int write_back, void* d_sum_or_null, void* d_mean_or_null, void* d_rgb8_or_null, void* stream);
+
+/* The same reduction spread over the ranks (what bench.py --gpus N and hobbyraytracer_b200/multigpu.py use).  Buffers that
+ * other processes map are library allocations: hrt_peer_alloc (zeroed cudaMalloc memory on the current device), hrt_peer_handle (its
+ * CUDA IPC handle, HRT_IPC_HANDLE_BYTES), hrt_peer_open (maps another process's handle into this one; cached per scene and closed
+ * with it).  Every rank holds its own film and the mappings of all other films and of the ROOT's output buffers; after the renders
+ * (a stream-ordered barrier between them and the reduction is the caller's: e.g. a one-word ncclAllReduce on the same stream) every
+ * rank calls hrt_film_resolve_slice on ITS share of the pixels: the lanes of all `films` (own first or not: integer sums commute) are
+ * added and resolved, and float sums / means / the 8-bit image of pixels [pix_first, pix_first + pix_count) are stored through the
+ * given pointers - the root's buffers - at their pixel offsets.  No rank gathers alone, nothing is staged; a second barrier tells the
+ * root that every slice has landed and the ranks that their films may be zeroed again. */
+void* hrt_peer_alloc(int64_t bytes);
+void  hrt_peer_free(void* p);
+int   hrt_peer_handle(void* p, void* out_handle);
+void* hrt_peer_open(hrt_scene* s, const void* handle);
+int   hrt_film_resolve_slice(hrt_scene* s, const void* const* films, int n_films, int width, int height, int spp, int pix_first, int pix_count,
+                             void* d_sum_or_null, void* d_mean_or_null, void* d_rgb8_or_null, void* stream);
 
 /* Introspection of a committed scene (tests, tooling): copies one device array of mesh `mesh_index` (world-list order of
  * first use) into `out` (may be NULL) and returns its size in bytes.  which: 0 reference-topology nodes (32 B each),

@@ -226,19 +226,20 @@ def test_render_matches_oracle_within_noise(orc, hrt, cache_dir, name):
 
 
 def eight_bit_case(name, cache_dir):
-    """-> scene, camera, oracle spp: the spp at which the oracle's own 8-bit noise is ~1.9 / 255 (measured: RMSE(A, B) at 256 spp is
-    3.2 on the shiny teapot, 2.0 on the balls, 3.7 on the big mesh: profiles/README.md r2j)"""
+    """-> scene, camera, oracle spp: enough for the oracle's own 8-bit noise to stay under the bound (measured on the CPU, oracle against
+    oracle: RMSE(A, B) at 256 spp each is 3.2 on the shiny teapot, 2.0 on the balls, 3.7 on the big mesh; shiny teapot at 384 spp against
+    4096 spp 2.18 - the GPU measured 2.17 against the same 384 - and at 768 spp 1.85)"""
     if name == "shiny_teapot":
-        sd, cam, _ = scenes.shiny_teapot_scene(cache_dir, n=24, env_w=256, env_h=128); return sd, cam, 384
+        sd, cam, _ = scenes.shiny_teapot_scene(cache_dir, n=24, env_w=256, env_h=128); return sd, cam, 768
     if name == "scattered_balls":
         sd, cam, _ = scenes.scattered_balls_scene(seed=42, grid=4); return sd, cam, 256
-    sd, cam, _ = scenes.big_mesh_scene(cache_dir, quads=120, env_w=256, env_h=128); return sd, cam, 512
+    sd, cam, _ = scenes.big_mesh_scene(cache_dir, quads=120, env_w=256, env_h=128); return sd, cam, 768
 
 
 @pytest.mark.parametrize("name", ["shiny_teapot", "scattered_balls", "big_mesh"])
 def test_eight_bit_image_against_oracle(orc, hrt, cache_dir, name):
     """SURVEY.md §8d, env / sky-lit configs (C2, C3, C5 style) at 480 x 270: the final 8-bit image (ACES + gamma) within 2 / 255 RMSE
-    of the CPU oracle's.  Spp on each side: the oracle at 256-512 (see eight_bit_case), the GPU at 4096 - its own noise then adds
+    of the CPU oracle's.  Spp on each side: the oracle at 256-768 (see eight_bit_case), the GPU at 4096 - its own noise then adds
     under 10 % to the oracle's, which is what the bound has to absorb."""
     sd, cam, spp_cpu = eight_bit_case(name, cache_dir)
     w, h, spp_gpu = 480, 270, 4096

@@ -23,6 +23,7 @@ BVH_REFERENCE, BVH_SAH, BVH_LBVH_GPU, BVH_LBVH_HOST = range(4)
 RENDER_MEGAKERNEL = 1
 RENDER_WAVEFRONT_V1 = 2
 RENDER_DEFOCUS = 4
+RENDER_RR = 8
 MESH_BORROW = 1
 
 

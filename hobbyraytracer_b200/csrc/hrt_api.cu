@@ -265,7 +265,11 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
     const int first = p->sample_first, count = p->sample_count > 0 ? p->sample_count : p->spp;
     const int max_depth = p->max_depth > 0 ? p->max_depth : 50;
     const bool mega = (p->flags & HRT_RENDER_MEGAKERNEL) != 0;
-    const bool v1 = (p->flags & HRT_RENDER_WAVEFRONT_V1) != 0;       // queue-everything wavefront with regeneration (kept for A/B)
+#if defined(HRT_WITH_V1_PIPELINE)
+    const bool v1 = (p->flags & HRT_RENDER_WAVEFRONT_V1) != 0;       // queue-everything wavefront with regeneration (A/B builds only)
+#else
+    const bool v1 = false;                                           // not compiled into the product: the flag selects the default pipeline
+#endif
     const unsigned long long total = (unsigned long long)npix * (unsigned long long)count;
     unsigned long long cap = wave_capacity();
     if (cap > total) cap = (total + 1023ull) / 1024ull * 1024ull;
@@ -276,7 +280,7 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
     j.width = p->width; j.height = p->height; j.npix = npix; j.max_depth = max_depth;
     const bool tiled = (p->width % 8 == 0) && (p->height % 4 == 0);
     j.tiles_x = tiled ? p->width / 8 : 0; j.tiles_y = tiled ? p->height / 4 : 0;
-    j.t_min = p->t_min > 0 ? p->t_min : 0.001f; j.seed = p->seed; j.rng_mode = p->rng_mode;
+    j.t_min = p->t_min > 0 ? p->t_min : 0.001f; j.seed = p->seed; j.rng_mode = p->rng_mode; j.rr = (p->flags & HRT_RENDER_RR) ? 1 : 0;
     j.s_first = first; j.s_count = count; j.capacity = (unsigned int)cap; j.film = d_film;
     DCamera dc = make_camera(*cam);
     if ((p->flags & HRT_RENDER_DEFOCUS) && cam->aperture > 0.0f) dc.lens_radius = cam->aperture / 2.0f;   // camera.h:29
@@ -294,7 +298,9 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
     if (mega) {
         launch_render_mega(s->d, j, dc, s->sm_count, st, &s->stats.launches);
     } else {
+#if defined(HRT_WITH_V1_PIPELINE)
         if (v1) launch_wave_init(j, dc, s->sm_count, st, &s->stats.launches);
+#endif
         int it = 0, issued = 0, retired = 0; bool done = false;
         bool secondary_heavy = s->last_secondary_heavy;      // start from what the previous render of this scene found
         auto retire = [&](int chunk) -> int {               // waits for the chunk, adds its kernel times, looks at its snapshot
@@ -321,12 +327,16 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
             cudaEvent_t* ev = s->events.data() + (size_t)EV_PER_CHUNK * (size_t)(issued % CTL_RING);
             for (int k = 0; k < CHUNK; ++k, ++it) {
                 CK(cudaEventRecord(ev[2 * k], st));
-                if (v1) launch_wave_trace(s->d, j, it, s->sm_count, st, &s->stats.launches);
-                else if (wide) launch_wave3_trace(s->d, j, dc, it, secondary_heavy, s->sm_count, st, &s->stats.launches);
+#if defined(HRT_WITH_V1_PIPELINE)
+                if (v1) launch_wave_trace(s->d, j, it, s->sm_count, st, &s->stats.launches); else
+#endif
+                if (wide) launch_wave3_trace(s->d, j, dc, it, secondary_heavy, s->sm_count, st, &s->stats.launches);
                 else launch_wave2_trace(s->d, j, dc, it, secondary_heavy, s->sm_count, st, &s->stats.launches);
                 CK(cudaEventRecord(ev[2 * k + 1], st));
-                if (v1) launch_wave_shade(s->d, j, dc, it, s->sm_count, st, &s->stats.launches);
-                else launch_wave2_shade(s->d, j, it, s->sm_count, st, &s->stats.launches);
+#if defined(HRT_WITH_V1_PIPELINE)
+                if (v1) launch_wave_shade(s->d, j, dc, it, s->sm_count, st, &s->stats.launches); else
+#endif
+                launch_wave2_shade(s->d, j, it, s->sm_count, st, &s->stats.launches);
             }
             CK(cudaEventRecord(ev[2 * CHUNK], st));
             CK(cudaMemcpyAsync(&s->h_ctl[issued % CTL_RING], j.ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, st));
@@ -650,7 +660,7 @@ CheckpointHeader checkpoint_header_of(const hrt_scene* s, const hrt_camera* cam,
     CheckpointHeader h; memset(&h, 0, sizeof(h));
     memcpy(h.magic, kCheckpointMagic, 8);
     h.width = p->width; h.height = p->height; h.spp = p->spp; h.samples_done = 0;
-    h.max_depth = p->max_depth > 0 ? p->max_depth : 50; h.rng_mode = p->rng_mode; h.flags_reserved = p->flags & HRT_RENDER_DEFOCUS;
+    h.max_depth = p->max_depth > 0 ? p->max_depth : 50; h.rng_mode = p->rng_mode; h.flags_reserved = p->flags & (HRT_RENDER_DEFOCUS | HRT_RENDER_RR);
     h.t_min = p->t_min > 0 ? p->t_min : 0.001f;
     h.seed = p->seed; h.camera_hash = fnv1a(cam, sizeof(*cam)); h.prim_count = (uint64_t)s->host.n_prims;
     return h;

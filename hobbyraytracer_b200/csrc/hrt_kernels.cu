@@ -277,6 +277,9 @@ __device__ __forceinline__ void write_camera_path(const WaveJob& j, const DCamer
 
 __device__ __forceinline__ unsigned long long min_ull(unsigned long long a, unsigned long long b) { return a < b ? a : b; }
 
+constexpr int SHADE_BLOCK = 256;
+
+#if defined(HRT_WITH_V1_PIPELINE)      // the r1b / r1c pipeline (every ray queued, regeneration in the shade pass): A/B builds only
 // ---- K1 (first fill) -------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(BLOCK) k_wave_init(WaveJob j, DCamera cam)
 {
@@ -334,7 +337,6 @@ __global__ void __launch_bounds__(BLOCK, HRT_TRACE_MIN_BLOCKS) k_wave_trace(DSce
 // ---- K4 + K3 + K1 + K5 ------------------------------------------------------------------------------------------------------
 // One queue-slot claim per BLOCK and pass of the loop (two returning atomics on two hot addresses): a per-warp claim
 // made every warp wait ~1.5 us for the round trip to L2 and serialised 260 k same-address atomics per pass (profiles/ r1b).
-constexpr int SHADE_BLOCK = 256;
 __global__ void __launch_bounds__(SHADE_BLOCK) k_wave_shade(DScene s, WaveJob j, DCamera cam, int q)
 {
     __shared__ unsigned int w_go[SHADE_BLOCK / 32], w_fresh[SHADE_BLOCK / 32];
@@ -399,6 +401,8 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave_shade(DScene s, WaveJob j,
         __syncthreads();                                                        // the next pass of the loop rewrites the shared counters
     }
 }
+
+#endif // HRT_WITH_V1_PIPELINE
 
 // ---- fused-primary wavefront (the default pipeline) ---------------------------------------------------------------------------
 // profiles/ r1c: on shiny_teapot 90 % of all rays are camera rays and 85 % of those leave the scene at once, yet every
@@ -619,6 +623,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j
     }
 }
 
+template <bool RR>
 __global__ void __launch_bounds__(SHADE_BLOCK) k_wave2_shade(DScene s, WaveJob j, int q)
 {
     __shared__ unsigned int w_go[SHADE_BLOCK / 32];
@@ -648,6 +653,7 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave2_shade(DScene s, WaveJob j
             go = shade_segment(s, h, r, atten, rad, key, bounce);
             if (rad.x != 0.0f || rad.y != 0.0f || rad.z != 0.0f) { result = result + rad; has_result = true; }
             go = go && (int)bounce + 1 < j.max_depth;                               // MAX_DEPTH reached: the partial sum stands (main.cpp:43,78)
+            if (RR) go = go && russian_roulette(atten, key, bounce);                // opt-in, separate instantiation: the default kernel is unchanged
             if (go) st = pack_state(sl, (int)bounce + 1, has_result);
             else if (has_result) film_add(j.film, pix, result, &c->clamped);                     // px += rayColour(...)  main.cpp:123
         }
@@ -757,6 +763,7 @@ __global__ void __launch_bounds__(BLOCK) k_render_mega(DScene s, WaveJob j, DCam
             ++rays;
             V3 rad; bool go = shade_segment(s, h, r, atten, rad, key, (uint32_t)b);
             if (rad.x != 0.0f || rad.y != 0.0f || rad.z != 0.0f) { result = result + rad; has_result = true; }
+            if (go && j.rr && b + 1 < j.max_depth) go = russian_roulette(atten, key, (uint32_t)b);
             if (!go) break;
         }
         if (has_result) film_add(j.film, pix, result, &j.ctl->clamped);
@@ -804,6 +811,7 @@ void launch_eval_batch(const DScene& s, const float4* d_rays, const Hit* d_hits,
     k_eval_batch<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, d_rays, d_hits, n, d_normal, d_uv, d_front); *launches += 1;
 }
 
+#if defined(HRT_WITH_V1_PIPELINE)
 void launch_wave_init(const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches)
 {
     k_wave_init<<<grid_for((long long)j.capacity, sm_count, 16), BLOCK, 0, st>>>(j, cam);
@@ -821,6 +829,7 @@ void launch_wave_shade(const DScene& s, const WaveJob& j, const DCamera& cam, in
     k_wave_shade<<<(int)(want < cap ? want : cap), SHADE_BLOCK, 0, st>>>(s, j, cam, it & 1); *launches += 1;
     }
 }
+#endif
 int wave2_trace_blocks(unsigned int capacity, int sm_count, int minb)
 {
     long long cap = (long long)capacity / (4ll * CLAIM * (BLOCK / 32));            // keeps the append margin below 1/4 of the queue
@@ -855,11 +864,12 @@ void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, i
     // Secondary rays: the phase kernel with per-lane refill where walks are long and uneven - scenes with meshes whose rays are mostly
     // secondary (teapot_scene 1253 -> 1611 Mrays/s) or whose meshes are large (big_mesh); elsewhere k_wave2_trace's own lock-step
     // pass is as good or better (B200 A/B r2f: shiny_teapot 8874 vs 8658, scattered_balls 5300 vs 3276, cornell_smoke 4070 vs 3626)
-    const int wsec = (s.refill_secondary && (secondary_heavy || s.big_mesh)) ? 1 : 0;
+    const bool force_wsec = getenv("HRT_FORCE_WIDE_SECONDARY") != nullptr, force_wtrace = getenv("HRT_FORCE_WIDE_PRIMARY") != nullptr;   // tests, sanitizer runs
+    const int wsec = ((s.refill_secondary && (secondary_heavy || s.big_mesh)) || force_wsec) ? 1 : 0;
     if (wsec) { k_wide_secondary<<<sm_count * HRT_WSEC_MIN_BLOCKS, BLOCK, 0, st>>>(s, j, it & 1); *launches += 1; }
     const bool lens = cam.lens_radius > 0.0f;
     const int q = it & 1;
-    if (s.big_mesh) {
+    if (s.big_mesh || force_wtrace) {
         const int blocks = wave2_trace_blocks(j.capacity, sm_count, HRT_WTRACE_MIN_BLOCKS);
         if (lens) k_wave2_trace<HRT_WTRACE_MIN_BLOCKS, true, true><<<blocks, BLOCK, 0, st>>>(s, j, cam, q, wsec);
         else k_wave2_trace<HRT_WTRACE_MIN_BLOCKS, false, true><<<blocks, BLOCK, 0, st>>>(s, j, cam, q, wsec);
@@ -876,7 +886,9 @@ void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, i
 void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches)
 {
     long long want = ((long long)j.capacity + SHADE_BLOCK - 1) / SHADE_BLOCK, cap = (long long)sm_count * 8;
-    k_wave2_shade<<<(int)(want < cap ? want : cap), SHADE_BLOCK, 0, st>>>(s, j, it & 1); *launches += 1;
+    if (j.rr) k_wave2_shade<true><<<(int)(want < cap ? want : cap), SHADE_BLOCK, 0, st>>>(s, j, it & 1);
+    else k_wave2_shade<false><<<(int)(want < cap ? want : cap), SHADE_BLOCK, 0, st>>>(s, j, it & 1);
+    *launches += 1;
 }
 void launch_render_mega(const DScene& s, const WaveJob& j, const DCamera& cam, int sm_count, cudaStream_t st, uint64_t* launches)
 {

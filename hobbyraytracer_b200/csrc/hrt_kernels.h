@@ -41,6 +41,7 @@ struct WaveJob {
     float t_min;
     uint64_t seed;
     int rng_mode;
+    int rr;                             // HRT_RENDER_RR: Russian roulette in the shade pass (hrt_shade.cuh)
     int s_first, s_count;
     unsigned int capacity;
     float4* rays[2];

@@ -18,7 +18,7 @@
 
 namespace hrt {
 
-enum { SLOT_SCATTER = 0, SLOT_BALL = 16, SLOT_MEDIUM = 0x10000 };
+enum { SLOT_SCATTER = 0, SLOT_RR = 8, SLOT_BALL = 16, SLOT_MEDIUM = 0x10000 };      // SLOT_BALL + rejection round stays below 0x10000
 constexpr uint32_t BOUNCE_CAMERA = 0xFFFFFFFFu;
 
 struct U4 { uint32_t x, y, z, w; };

@@ -180,6 +180,23 @@ HRT_HDN inline bool shade_segment(const DScene& s, const Hit& h, Ray& r, V3& att
     return true;
 }
 
+// ---- Russian roulette (opt-in, HRT_RENDER_RR): the reference has none (main.cpp:43-76 runs every path to MAX_DEPTH or a miss) ------
+// After the scatter of segment `bounce` (0-based), from the third segment on, the path survives with probability
+// p = clamp(max(attenuation), 0.05, 1) and its attenuation is divided by p: the estimator is unchanged in expectation, dim paths stop
+// early.  The draw is its own Philox slot, so no other random number of the path moves.  Returns false when the path is cut.
+constexpr uint32_t RR_FIRST_BOUNCE = 2;
+HRT_HD bool russian_roulette(V3& atten, const RngKey& key, uint32_t bounce)
+{
+    if (bounce < RR_FIRST_BOUNCE) return true;
+    float p = fmaxf(atten.x, fmaxf(atten.y, atten.z));
+    p = p < 0.05f ? 0.05f : (p > 1.0f ? 1.0f : p);
+    if (!(p < 1.0f)) return true;                                             // (also: NaN attenuation goes on like the reference's)
+    const float xi = (float)rng_draw(key, bounce, SLOT_RR).x * 2.3283064365386963e-10f;   // [0, 1): plain uniform whatever the rng mode
+    if (xi >= p) return false;
+    atten = atten / p;
+    return true;
+}
+
 // ---- camera: getRay camera.h:32-39 (the lens offset is forced to zero there) ---------------------------------------------
 // lens_word: a spare word of the camera-jitter draw, used only under HRT_RENDER_DEFOCUS (c.lens_radius > 0) for
 // glm::circularRand(lensRadius) (random.inl:281-287): a = linearRand(0, 2 pi), rd = (cos a, sin a) * Radius

@@ -115,12 +115,18 @@ typedef struct hrt_render_params {
 } hrt_render_params;
 
 #define HRT_RENDER_MEGAKERNEL 1   /* one thread per path instead of the persistent wavefront (debug/validation) */
-#define HRT_RENDER_WAVEFRONT_V1 2  /* every camera ray goes through the queues (the r1b/r1c pipeline, kept for A/B runs) */
+#define HRT_RENDER_WAVEFRONT_V1 2  /* every camera ray goes through the queues (the r1b/r1c pipeline): only in libraries built with
+                                      -DHRT_WITH_V1_PIPELINE (A/B builds); the product ignores the flag */
 #define HRT_RENDER_DEFOCUS 4       /* opt-in: the lens sampling camera.h:34 has commented out ("TODO: Add back in randomness"):
                                       rd = glm::circularRand(lensRadius), offset = u*rd.x + v*rd.y, lensRadius = aperture/2
                                       (camera.h:29).  Without the flag - and with aperture == 0 - the offset is zero like
                                       the reference's; the lens draw uses a spare word of the camera-jitter Philox call,
                                       so no other random number of the path changes. */
+
+#define HRT_RENDER_RR 8            /* opt-in Russian roulette: the reference has none (main.cpp:43-76 walks every path to MAX_DEPTH or
+                                      a miss).  From the third segment on a path survives its scatter with probability
+                                      p = clamp(max(attenuation), 0.05, 1) and carries attenuation / p: same expectation, fewer rays per
+                                      sample on closed scenes.  Own Philox slot: with the flag off the film is bit-identical to before. */
 
 typedef struct hrt_stats {
     uint64_t rays;            /* closest-hit queries issued (= world->hit calls of main.cpp:45)      */

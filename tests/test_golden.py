@@ -135,3 +135,56 @@ def test_gpu_render_matches_reference_fixture_within_noise(hrt):
     assert abs(mg / mr - 1) < 0.03, (mg, mr)
     rays = sc.stats().rays
     assert abs(rays / float(fx["rays_a"]) - 1) < 0.01, (rays, int(fx["rays_a"]))
+
+
+# ---- C5 at full size: the 10,488,200-triangle mesh against the unmodified reference ------------------------------------------------
+def _bigmesh_case():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden_bigmesh", os.path.join(GOLD, "make_golden_bigmesh.py"))
+    mod = importlib.util.module_from_spec(spec); spec.loader.exec_module(mod)
+    import zlib
+    fx = np.load(os.path.join(GOLD, "trace_bigmesh.npz"))
+    sd, rays = mod.inputs()
+    assert int(fx["quads"]) == mod.QUADS and int(fx["n_rays"]) == len(rays) and np.uint32(zlib.crc32(rays.tobytes())) == fx["rays_crc"]
+    return sd, rays, fx, int(fx["seed"])
+
+
+def _same_as_reference(out, fx):
+    assert np.array_equal(out["prim"], fx["prim"]), f"{int((out['prim'] != fx['prim']).sum())} primitive ids differ from the reference's"
+    assert np.array_equal(bits(out["t"]), bits(fx["t"]))
+    assert (fx["prim"] != abi.MISS).mean() > 0.25
+
+
+def test_bigmesh_golden_on_the_cpu():
+    """north_star gate (1) at C5's size without a GPU: the product's host builders + device headers compiled for the CPU (tests/hostsim),
+    two-child walk and 8-wide walk, against (prim, t) of 2^18 rays of the 0xC0FFEE batch traced by the UNMODIFIED reference
+    (tests/golden/make_golden_bigmesh.py: triangle.cpp:57-131 under bvh.cpp:69-78) on the 10,488,200-triangle mesh."""
+    import ctypes as C
+    import subprocess
+    from conftest import ROOT
+    subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "tests", "hostsim")], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    hsim = abi.Lib(os.path.join(ROOT, "tests", "hostsim", "_build", "libhrt_hostsim.so"), "hsim_")
+    hsim._sig("trace_batch_wide", C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p])
+    sd, rays, fx, seed = _bigmesh_case()
+    sc = sd.build(hsim, abi.BVH_SAH, seed)
+    _same_as_reference(sc.trace(rays, extras=False), fx)
+    prim = np.empty(len(rays), np.uint32); t = np.empty(len(rays), np.float32)
+    hsim.check(hsim.fn("trace_batch_wide")(sc.h, rays.ctypes.data, len(rays), prim.ctypes.data, t.ctypes.data, 0, None), "trace_batch_wide")
+    _same_as_reference(dict(prim=prim, t=t), fx)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", [abi.BVH_SAH, abi.BVH_REFERENCE])
+def test_bigmesh_golden_on_the_gpu(hrt, mode):
+    """The same on the B200 through the C ABI: ids and t bit for bit, in the reference's visiting order and through the SAH + 8-wide trees
+    (the ray-batch kernel of bench.py --workload raybatch).  HRT_BVH_LBVH_GPU orders equal sort keys of the reference topology stably
+    (include/hrt.h) and may differ from this golden in rays that start within t_min of the surface; it is pinned against its host mirror."""
+    sd, rays, fx, seed = _bigmesh_case()
+    sc = sd.build(hrt, mode, seed)
+    _same_as_reference(sc.trace(rays, extras=False), fx)
+    if mode == abi.BVH_SAH:
+        os.environ["HRT_NO_WIDE"] = "1"
+        try:
+            _same_as_reference(sc.trace(rays, extras=False), fx)            # the two-child walk of the same trees
+        finally:
+            del os.environ["HRT_NO_WIDE"]

@@ -228,21 +228,22 @@ def test_render_matches_oracle_within_noise(orc, hrt, cache_dir, name):
 def eight_bit_case(name, cache_dir):
     """-> scene, camera, oracle spp: enough for the oracle's own 8-bit noise to stay under the bound (measured on the CPU, oracle against
     oracle: RMSE(A, B) at 256 spp each is 3.2 on the shiny teapot, 2.0 on the balls, 3.7 on the big mesh; shiny teapot at 384 spp against
-    4096 spp 2.18 - the GPU measured 2.17 against the same 384 - and at 768 spp 1.85)"""
+    4096 spp 2.18 - the GPU measured 2.17 against the same 384 - and at 768 spp 1.85; the big mesh, whose bright-window reflections are
+    heavy tailed, 768 against 2048 spp 2.42 - the GPU 2.52 - and 1024 against 2048 still 2.28: it takes 2048 spp)"""
     if name == "shiny_teapot":
-        sd, cam, _ = scenes.shiny_teapot_scene(cache_dir, n=24, env_w=256, env_h=128); return sd, cam, 768
+        sd, cam, _ = scenes.shiny_teapot_scene(cache_dir, n=24, env_w=256, env_h=128); return sd, cam, 1024
     if name == "scattered_balls":
         sd, cam, _ = scenes.scattered_balls_scene(seed=42, grid=4); return sd, cam, 256
-    sd, cam, _ = scenes.big_mesh_scene(cache_dir, quads=120, env_w=256, env_h=128); return sd, cam, 768
+    sd, cam, _ = scenes.big_mesh_scene(cache_dir, quads=120, env_w=256, env_h=128); return sd, cam, 2048
 
 
 @pytest.mark.parametrize("name", ["shiny_teapot", "scattered_balls", "big_mesh"])
 def test_eight_bit_image_against_oracle(orc, hrt, cache_dir, name):
     """SURVEY.md §8d, env / sky-lit configs (C2, C3, C5 style) at 480 x 270: the final 8-bit image (ACES + gamma) within 2 / 255 RMSE
-    of the CPU oracle's.  Spp on each side: the oracle at 256-768 (see eight_bit_case), the GPU at 4096 - its own noise then adds
-    under 10 % to the oracle's, which is what the bound has to absorb."""
+    of the CPU oracle's.  Spp on each side: the oracle at 256-2048 (see eight_bit_case), the GPU at 8192 - its own noise then adds
+    little to the oracle's, which is what the bound has to absorb."""
     sd, cam, spp_cpu = eight_bit_case(name, cache_dir)
-    w, h, spp_gpu = 480, 270, 4096
+    w, h, spp_gpu = 480, 270, 8192
     c = scenes.camera_for(cam, w, h)
     A, rays_a = sd.build(orc, 0, 3).render_f32(c, w, h, spp_cpu, seed=31)
     a8 = np.empty((h, w, 3), np.uint8)
@@ -266,9 +267,14 @@ def test_wavefront_equals_megakernel_and_sample_split(hrt, cache_dir):
         wf, _ = g.render(c, w, h, spp, seed=9)
         mk, _ = g.render(c, w, h, spp, seed=9, flags=abi.RENDER_MEGAKERNEL)
         assert np.array_equal(bits(wf), bits(mk)), "wavefront pipeline differs from the one-thread-per-path loop"
-        v1, _ = g.render(c, w, h, spp, seed=9, flags=abi.RENDER_WAVEFRONT_V1)
-        assert np.array_equal(bits(wf), bits(v1)), "fused-primary pipeline differs from the every-ray-queued pipeline"
-        assert g.stats().rays % 3 == 0              # three renders of the same paths counted the same rays
+        assert g.stats().rays % 2 == 0              # two renders of the same paths counted the same rays
+        # opt-in Russian roulette: off by default (the two renders above), the same bits from both pipelines when on, fewer rays
+        rays_plain = g.stats().rays // 2
+        rr, _ = g.render(c, w, h, spp, seed=9, flags=abi.RENDER_RR)
+        rays_rr = g.stats().rays - 2 * rays_plain
+        rm, _ = g.render(c, w, h, spp, seed=9, flags=abi.RENDER_RR | abi.RENDER_MEGAKERNEL)
+        assert np.array_equal(bits(rr), bits(rm)) and not np.array_equal(bits(rr), bits(wf))
+        assert rays_rr < 0.8 * rays_plain, (rays_rr, rays_plain)
         # samples are keyed by (pixel, global sample index) and the film adds integers: the wavefront capacity (hence the
         # order in which paths start and finish) does not change a single bit
         for cap in (1024, 5000):
@@ -284,6 +290,58 @@ def test_wavefront_equals_megakernel_and_sample_split(hrt, cache_dir):
     ref = sd.build(hrt, abi.BVH_REFERENCE, 3).render(c, w, h, spp, seed=9)[0]
     fast = sd.build(hrt, abi.BVH_SAH, 3).render(c, w, h, spp, seed=9)[0]
     assert np.array_equal(bits(ref), bits(fast)), "SAH-order render differs from reference-order render"
+
+
+@pytest.mark.parametrize("name", ["teapot_scene", "cornell_smoke"])
+def test_russian_roulette_is_unbiased(orc, hrt, cache_dir, name):
+    """HRT_RENDER_RR against the oracle, which has no roulette (main.cpp:43-76): same image within the noise floor (the roulette adds
+    variance: the GPU renders 4 x the oracle's spp), global mean within 0.5 % or the oracle's own spread, rays per sample down."""
+    sd, cam, w, h, spp = render_case(name, cache_dir)
+    c = scenes.camera_for(cam, w, h)
+    o = sd.build(orc, 0, 3)
+    A, rays_a = o.render_f32(c, w, h, spp, seed=101); B, _ = o.render_f32(c, w, h, spp, seed=202)
+    A /= spp; B /= spp
+    ok = np.isfinite(A).all(-1) & np.isfinite(B).all(-1)
+    lim = float(np.percentile(A[ok], 99.9))
+    g = sd.build(hrt, abi.BVH_SAH, 3)
+    S, _ = g.render(c, w, h, 4 * spp, seed=7, flags=abi.RENDER_RR)
+    st = g.stats()
+    G = S / (4 * spp)
+    a, b, gg = np.minimum(A, lim), np.minimum(B, lim), np.minimum(G, lim)
+    rmse = lambda x, y: float(np.sqrt(np.mean((x[ok] - y[ok]) ** 2)))
+    assert rmse(gg, a) <= 1.1 * rmse(a, b), (rmse(gg, a), rmse(a, b))
+    ma, mb, mg = a[ok].mean(), b[ok].mean(), gg[ok].mean()
+    assert abs(mg - 0.5 * (ma + mb)) <= max(0.005 * ma, 3 * abs(ma - mb)), (ma, mb, mg)
+    worst, _ = block_gate(a, b, gg, ok)
+    assert worst <= 1.0, worst
+    assert st.rays / st.paths < 0.75 * rays_a / (w * h * spp), (st.rays / st.paths, rays_a / (w * h * spp))
+
+
+@pytest.mark.parametrize("case", ["teapot_scene", "cornell_smoke", "scattered_balls", "instances"])
+def test_wide_kernels_equal_megakernel(hrt, cache_dir, case):
+    """The kernels that walk the 8-wide trees — k_wide_secondary (phases + per-lane refill), k_wave2_trace<.., WIDE> (phased walk of a
+    claim) and the pending list + k_wave3_resolve behind them — are picked by the host from scene statistics (large meshes, many
+    secondary rays).  Here they are forced onto small scenes of every kind: the film must equal the one-thread-per-path loop over the
+    two-child trees bit for bit."""
+    if case == "instances":
+        sd = mesh_scene(16, ops=OPS[6]); m = sd.material(abi.MAT_METAL, (0.8, 0.8, 0.8), p0=0.1)
+        sd.add(sd.sphere((2, 1, 0), 0.7, m), OPS[1]); sd.add(sd.box((-2, 1, 0), (1, 2, 1), m), OPS[3]); sd.background = sd.solid((0.7, 0.8, 1.0))
+        cam = dict(position=(0, 2, 7), look_at=(0, 1, 0), up=(0, 1, 0), vfov_deg=50, aperture=0.0, focal_distance=7)
+        w, h, spp = 64, 48, 16
+    else:
+        sd, cam, w, h, spp = render_case(case, cache_dir); w, h, spp = 64, 48, 16
+    c = scenes.camera_for(cam, w, h)
+    g = sd.build(hrt, abi.BVH_SAH, 3)
+    mk, _ = g.render(c, w, h, spp, seed=9, flags=abi.RENDER_MEGAKERNEL)
+    for env in (("HRT_FORCE_WIDE_SECONDARY",), ("HRT_FORCE_WIDE_PRIMARY",), ("HRT_FORCE_WIDE_SECONDARY", "HRT_FORCE_WIDE_PRIMARY")):
+        for e in env:
+            os.environ[e] = "1"
+        try:
+            wf, _ = g.render(c, w, h, spp, seed=9)
+        finally:
+            for e in env:
+                del os.environ[e]
+        assert np.array_equal(bits(wf), bits(mk)), (case, env)
 
 
 def test_film_is_split_invariant(hrt, cache_dir):

@@ -126,6 +126,7 @@ class Lib:
         self._sig("scene_set_tagged", i, [_vp, i], required=False)
         self._sig("trace_batch", i, [_vp, _vp, i64, _vp, _vp, _vp, _vp, _vp, u64])
         self._sig("trace_batch_device", i, [_vp, _vp, i64, _vp, _vp, u64, _vp], required=False)
+        self._sig("trace_batch_static", i, [_vp, _vp, i64, _vp, _vp, u64, _vp], required=False)
         # product-only
         self._sig("abi_version", i, [], required=False)
         self._sig("trim", None, [], required=False)

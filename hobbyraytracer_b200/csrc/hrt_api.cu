@@ -535,6 +535,27 @@ int hrt_trace_batch_device(hrt_scene* s, const void* d_rays, int64_t n, void* d_
     return 0;
 }
 
+// hrt_trace_batch_device without any allocation: the scratch is a file-scope device array of hrt_kernels.cu (include/hrt.h).
+// Nothing here calls cudaMalloc / cudaFree or an allocating library routine; calls share the array and must not overlap on one GPU.
+int hrt_trace_batch_static(hrt_scene* s, const void* d_rays, int64_t n, void* d_prim_id, void* d_t, uint64_t rng_seed, void* stream)
+{
+    if (!s || (n > 0 && (!d_rays || !d_prim_id || !d_t)) || n < 0) { g_err = "bad argument"; return HRT_ERR_ARG; }
+    if (!s->host.committed) { g_err = "scene not committed"; return HRT_ERR_STATE; }
+    static_assert(HRT_TRACE_BATCH_STATIC_MAX == HRT_STATIC_BATCH_MAX, "include/hrt.h and hrt_kernels.h disagree on the static scratch size");
+    if (n > HRT_TRACE_BATCH_STATIC_MAX) {
+        g_err = "hrt_trace_batch_static: " + std::to_string((long long)n) + " rays exceed the static scratch of HRT_TRACE_BATCH_STATIC_MAX = "
+              + std::to_string((long long)HRT_TRACE_BATCH_STATIC_MAX) + " rays per call (split the batch or use hrt_trace_batch_device)";
+        return HRT_ERR_ARG;
+    }
+    if (n == 0) return 0;
+    CK(cudaSetDevice(s->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : s->stream;
+    cudaError_t e = launch_trace_batch_static(s->d, s->device, (const float4*)d_rays, n, (uint32_t*)d_prim_id, (float*)d_t, rng_seed, s->sm_count, st, &s->stats.launches);
+    if (e != cudaSuccess) { g_err = std::string("hrt_trace_batch_static: ") + cudaGetErrorString(e); return HRT_ERR_CUDA; }
+    s->stats.rays += (uint64_t)n;
+    return 0;
+}
+
 int hrt_trace_batch(hrt_scene* s, const float* rays, int64_t n, uint32_t* prim_id, float* t, float* normal, float* uv, uint8_t* front, uint64_t rng_seed)
 {
     if (!s || (n > 0 && (!rays || !prim_id || !t)) || n < 0) { g_err = "bad argument"; return HRT_ERR_ARG; }

@@ -16,6 +16,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdlib>
+#include <mutex>
 
 #include "hrt_kernels.h"
 #include "hrt_shade.cuh"
@@ -791,6 +792,43 @@ void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit*
     if (!s.wide || getenv("HRT_NO_WIDE")) { k_trace_batch_plain<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed); *launches += 1; return; }
     k_trace_batch<<<grid_for(n, sm_count, HRT_BATCH_MIN_BLOCKS), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed, d_counter, pend);
     k_resolve_batch<<<sm_count * 2, BLOCK, 0, st>>>(s, d_rays, d_hits, seed, pend); *launches += 2;
+}
+// ---- hrt_trace_batch_static: the ray batch without any allocation -------------------------------------------------------------------
+// The scratch of k_trace_batch / k_resolve_batch / k_split_hits (hit records, hand-out counter, pending list) lives in one file-scope
+// device array instead of cudaMalloc memory, for callers that must not allocate (CUDA graph capture, serving loops).  Every GPU that
+// loads the library holds the array until the process exits; all calls share it (calls that overlap on one GPU race).
+//   [0, 256)                      control words: hand-out counter at byte 0, pending count at byte 64 (both zeroed by every call)
+//   [256, 256 + 16 n_max)         hit records (16 B per ray; every record of a call is written before it is read)
+//   [256 + 16 n_max, + 4 n_max)   pending list
+static __device__ __align__(256) unsigned char g_static_scratch[256 + (size_t)HRT_STATIC_BATCH_MAX * (sizeof(Hit) + sizeof(unsigned int))];
+// In host code `g_static_scratch` is only a handle for the runtime, not a device address: the address is looked up once per device,
+// with that device current, and cached here.
+static unsigned char* g_static_scratch_ptr[HRT_STATIC_MAX_DEVICES];
+static std::mutex g_static_scratch_mu;
+
+cudaError_t launch_trace_batch_static(const DScene& s, int device, const float4* d_rays, long long n, uint32_t* d_prim, float* d_t, uint64_t seed,
+                                      int sm_count, cudaStream_t st, uint64_t* launches)
+{
+    if (device < 0 || device >= HRT_STATIC_MAX_DEVICES || n < 0 || n > HRT_STATIC_BATCH_MAX) return cudaErrorInvalidValue;
+    unsigned char* base;
+    {
+        std::lock_guard<std::mutex> lk(g_static_scratch_mu);
+        base = g_static_scratch_ptr[device];
+        if (!base) {                                                              // set-up, once per device (the caller made `device` current)
+            void* p = nullptr;
+            cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+            if (e != cudaSuccess) return e;
+            if (!p) return cudaErrorInvalidSymbol;
+            base = g_static_scratch_ptr[device] = (unsigned char*)p;
+        }
+    }
+    unsigned long long* counter = (unsigned long long*)base;
+    unsigned int* pend_count = (unsigned int*)(base + 64);
+    Hit* hits = (Hit*)(base + 256);
+    unsigned int* pend_idx = (unsigned int*)(base + 256 + (size_t)HRT_STATIC_BATCH_MAX * sizeof(Hit));
+    launch_trace_batch(s, d_rays, n, hits, seed, counter, pend_idx, pend_count, sm_count, st, launches);
+    launch_split_hits(hits, n, d_prim, d_t, sm_count, st, launches);
+    return cudaGetLastError();
 }
 void launch_texture_eval(const DScene& s, int tex, const float* d_in, long long n, float* d_out, int sm_count, cudaStream_t st, uint64_t* launches)
 {

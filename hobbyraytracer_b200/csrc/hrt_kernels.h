@@ -56,6 +56,12 @@ struct WaveJob {
 // d_pend_idx (n entries) / d_pend_count (one word): scratch for the rays that need pass 2 (hrt_wide.cuh)
 void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit* d_hits, uint64_t seed, unsigned long long* d_counter,
                         unsigned int* d_pend_idx, unsigned int* d_pend_count, int sm_count, cudaStream_t st, uint64_t* launches);
+// The same batch with its scratch in a file-scope device array of hrt_kernels.cu (no allocation; at most HRT_STATIC_BATCH_MAX rays;
+// `device` must be current).  Returns the CUDA status of the set-up (cudaGetSymbolAddress, once per device) and of the launches.
+#define HRT_STATIC_BATCH_MAX (1ll << 20)
+#define HRT_STATIC_MAX_DEVICES 64
+cudaError_t launch_trace_batch_static(const DScene& s, int device, const float4* d_rays, long long n, uint32_t* d_prim, float* d_t, uint64_t seed,
+                                      int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_texture_eval(const DScene& s, int tex, const float* d_in, long long n, float* d_out, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_scatter_batch(const DScene& s, int material, const float* d_in, const uint8_t* d_front, long long n, uint64_t seed, int rng_mode, float* d_out,
                           int sm_count, cudaStream_t st, uint64_t* launches);

@@ -223,6 +223,18 @@ int hrt_trace_batch(hrt_scene* s, const float* rays, int64_t n, uint32_t* prim_i
 int hrt_trace_batch_device(hrt_scene* s, const void* d_rays, int64_t n, void* d_prim_id, void* d_t,
                            uint64_t rng_seed, void* stream);
 
+/* hrt_trace_batch_device for callers that must not allocate device memory (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.  Same inputs, outputs
+ * and results as hrt_trace_batch_device, but the scratch of the batch kernels (16 B hit record + 4 B pending-list slot per ray, 256 B
+ * of control words) is a file-scope device array of HRT_TRACE_BATCH_STATIC_MAX rays (20 MiB + 256 B, held by every GPU that loads the
+ * library until the process exits) instead of cudaMalloc memory.  The call never calls cudaMalloc / cudaFree or an allocating library
+ * routine; its first use on a device looks the array's address up (cudaGetSymbolAddress) - make that call outside a graph capture.
+ * n > HRT_TRACE_BATCH_STATIC_MAX is HRT_ERR_ARG (split the batch).  All calls - of all scenes on that GPU - share the array: the
+ * control words are cleared by every call, and calls that overlap on the GPU (different streams, no ordering) race.               */
+#define HRT_TRACE_BATCH_STATIC_MAX (1 << 20)
+int hrt_trace_batch_static(hrt_scene* s, const void* d_rays, int64_t n, void* d_prim_id, void* d_t,
+                           uint64_t rng_seed, void* stream);
+
 /* The shading half of the path on caller-supplied batches (parity entries, like hrt_trace_batch for hit()):
  * hrt_texture_eval: Texture::colourValue(u, v, p) of texture `texture` (texture.h:3-7, texture.cpp:17-97); uvp: n x 5 floats
  *   (u, v, p.xyz), out_rgb: n x 3.

@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <atomic>
 #include <mutex>
 #include <unordered_map>
 #include <string>
@@ -25,6 +26,7 @@ using namespace hrt;
 namespace {
 thread_local std::string g_err;
 int g_device = 0;
+std::atomic<bool> g_last_secondary_heavy{false};      // kernel choice of the last render of the process: where a new scene starts (render_into)
 
 #define CK(call)                                                                                          \
     do {                                                                                                  \
@@ -40,7 +42,7 @@ int g_device = 0;
 struct BlockCache {
     struct Block { int device; size_t bytes; void* p; };
     std::mutex m; std::vector<Block> blocks; size_t total = 0;
-    static constexpr size_t MAX_TOTAL = size_t(1) << 30, MAX_BLOCKS = 256;
+    static constexpr size_t MAX_TOTAL = size_t(32) << 30, MAX_BLOCKS = 1024;     // C5: 2.9 GB of scene + 1 GB of builder scratch per scene in flight
     void* take(int device, size_t bytes)
     {
         std::lock_guard<std::mutex> lock(m);
@@ -65,6 +67,17 @@ struct BlockCache {
     }
 };
 BlockCache g_blocks;
+
+} // namespace
+namespace hrt {
+cudaError_t pool_alloc(int device, size_t bytes, void** p)
+{
+    *p = g_blocks.take(device, bytes);
+    return *p ? cudaSuccess : cudaMalloc(p, bytes);
+}
+void pool_give(int device, size_t bytes, void* p) { if (p) g_blocks.give(device, bytes, p); }
+} // namespace hrt
+namespace {
 
 struct DevBuf {                       // scoped device scratch: freed on every exit path
     void* p = nullptr;
@@ -102,7 +115,7 @@ struct hrt_scene {
     int device = 0, sm_count = 148;
     cudaStream_t stream = nullptr;
     std::vector<void*> scene_allocs;
-    std::unordered_map<void*, size_t> scene_alloc_bytes;        // sizes of the uploaded arrays (device-built ones are not listed)
+    std::unordered_map<void*, size_t> scene_alloc_bytes;        // sizes of the scene's pool blocks (uploads and device-built arrays)
     size_t scene_bytes = 0, h2d_bytes = 0; double ms_build_upload = 0;
     // persistent-wavefront working set
     WaveJob job{};
@@ -117,7 +130,7 @@ struct hrt_scene {
     unsigned int* tb_pend = nullptr;                            // tb_capacity indices + 1 count: rays left to pass 2
     unsigned long long* d_counter = nullptr;                    // ray hand-out counter of k_trace_batch
     hrt_stats stats{};
-    bool last_secondary_heavy = false;
+    bool last_secondary_heavy = false, have_secondary_prior = false;   // kernel choice of the previous render of this scene (render_into)
     double ms_build_gpu = 0; int bvh_fallbacks = 0;             // HRT_BVH_LBVH_GPU: upload + device build time, meshes handed back to the host builder
     std::vector<DMesh> meshes_view;                             // host copy of DScene::meshes (hrt_scene_mesh_array)
     std::vector<std::pair<cudaIpcMemHandle_t, void*>> peers;    // peer films opened through CUDA IPC (closed with the scene)
@@ -240,7 +253,7 @@ unsigned int wave_capacity()
 {
     const char* e = getenv("HRT_WAVE_CAPACITY");
     long long v = e ? atoll(e) : 0;
-    if (v < 1024) v = 4ll << 20;
+    if (v < 1024) v = 32ll << 20;            // entries per queue (148 B each): B200 A/B r2o 4 / 8 / 16 / 32 Mi: C5 1879 / 2236 / 2474 / 2611, C1 1603 / 1715 / 1790 / 1837 Mrays/s
     if (v > (1ll << 30)) v = 1ll << 30;
     return (unsigned int)v;
 }
@@ -302,30 +315,40 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
         if (v1) launch_wave_init(j, dc, s->sm_count, st, &s->stats.launches);
 #endif
         int it = 0, issued = 0, retired = 0; bool done = false;
-        bool secondary_heavy = s->last_secondary_heavy;      // start from what the previous render of this scene found
+        // Kernel choice (lock-step pass vs per-lane refill for the secondary rays, register build of the camera-path kernel) follows the
+        // measured secondary rays per camera path.  It starts from what the previous render of this scene found; a scene that has not
+        // been rendered yet starts from the last finding of the process (a host that rebuilds its scene per frame) and looks at its
+        // first TWO iterations before it queues more: r2o launch list of teapot_scene - 24 iterations with the wrong kernel at the
+        // start of every new scene were 29 % of the kernel time (3.3 ms per pass instead of 0.9).
+        const bool have_prior = s->have_secondary_prior;
+        bool secondary_heavy = have_prior ? s->last_secondary_heavy : g_last_secondary_heavy.load();
+        int chunk_len[CTL_RING] = {0}, chunk_end_it[CTL_RING] = {0};
         auto retire = [&](int chunk) -> int {               // waits for the chunk, adds its kernel times, looks at its snapshot
             cudaEvent_t* ev = s->events.data() + (size_t)EV_PER_CHUNK * (size_t)(chunk % CTL_RING);
             CK(cudaEventSynchronize(ev[2 * CHUNK + 1]));
             float ms = 0;
-            for (int k = 0; k < CHUNK; ++k) {
+            for (int k = 0; k < chunk_len[chunk % CTL_RING]; ++k) {
                 CK(cudaEventElapsedTime(&ms, ev[2 * k], ev[2 * k + 1])); s->stats.ms_trace += ms;
                 CK(cudaEventElapsedTime(&ms, ev[2 * k + 1], ev[2 * k + 2])); s->stats.ms_shade += ms;
             }
             const WaveCtl& c = s->h_ctl[chunk % CTL_RING];
-            const int o = (chunk * CHUNK + CHUNK) & 1;       // queue the last shade pass of the chunk filled
+            const int o = chunk_end_it[chunk % CTL_RING] & 1; // queue the last shade pass of the chunk filled
             const unsigned long long handed = c.next_path < c.total_paths ? c.next_path : c.total_paths;
             if (!v1 && c.next_path > 0) {                    // fused-primary: secondary rays per camera path so far (claims are CLAIM paths)
                 const double paths = (double)handed * (double)total / (double)(c.total_paths ? c.total_paths : 1);
                 secondary_heavy = (double)c.rays > 0.75 * paths;
-                s->last_secondary_heavy = secondary_heavy;
+                s->last_secondary_heavy = secondary_heavy; s->have_secondary_prior = true;
+                g_last_secondary_heavy.store(secondary_heavy);
             }
             if (v1 ? (c.n_front[o] == 0 && handed == c.base[o] && handed == c.total_paths) : (c.n_front[o] == 0 && handed == c.total_paths)) done = true;
             return 0;
         };
         while (!done) {
-            if (issued - retired >= CTL_RING - 1) { rc = retire(retired++); if (rc < 0) return rc; if (done) break; }
+            if (issued - retired >= CTL_RING - 1 || (issued == 1 && !have_prior)) { rc = retire(retired++); if (rc < 0) return rc; if (done) break; }
             cudaEvent_t* ev = s->events.data() + (size_t)EV_PER_CHUNK * (size_t)(issued % CTL_RING);
-            for (int k = 0; k < CHUNK; ++k, ++it) {
+            const int len = (issued == 0 && !have_prior) ? 2 : CHUNK;
+            chunk_len[issued % CTL_RING] = len; chunk_end_it[issued % CTL_RING] = it + len;
+            for (int k = 0; k < len; ++k, ++it) {
                 CK(cudaEventRecord(ev[2 * k], st));
 #if defined(HRT_WITH_V1_PIPELINE)
                 if (v1) launch_wave_trace(s->d, j, it, s->sm_count, st, &s->stats.launches); else
@@ -338,7 +361,7 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
 #endif
                 launch_wave2_shade(s->d, j, it, s->sm_count, st, &s->stats.launches);
             }
-            CK(cudaEventRecord(ev[2 * CHUNK], st));
+            CK(cudaEventRecord(ev[2 * len], st));
             CK(cudaMemcpyAsync(&s->h_ctl[issued % CTL_RING], j.ctl, sizeof(WaveCtl), cudaMemcpyDeviceToHost, st));
             CK(cudaEventRecord(ev[2 * CHUNK + 1], st));
             CK(cudaGetLastError());
@@ -470,7 +493,7 @@ int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed)
         MeshSource src;
         if (sh.indexed) { src.indexed = true; src.pos = sh.V(); src.nrm = sh.N(); src.uv = sh.T(); src.idx = sh.I(); src.n_vert = sh.n_vert; }
         else { src.pos = sh.pos.data(); src.nrm = sh.nrm.data(); src.uv = sh.uv.data(); }
-        if (!build_mesh_gpu(src, sh.n_tri, seed, shape, s->stream, s->scene_allocs, dev_bytes, b, berr, &s->stats.launches)) {
+        if (!build_mesh_gpu(src, sh.n_tri, seed, shape, s->stream, s->scene_allocs, s->scene_alloc_bytes, dev_bytes, b, berr, &s->stats.launches)) {
             g_err = "device BVH build failed: " + berr; free_scene_device(s); return HRT_ERR_CUDA;
         }
         sh.gpu_pending = false;

@@ -297,10 +297,15 @@ __global__ void k_wide_link(const int* __restrict__ first, int n_items, int base
     }
 }
 
-struct Tmp {
-    std::vector<void*> ptrs;
-    ~Tmp() { for (void* p : ptrs) cudaFree(p); }
-    template <class T> bool get(T*& p, size_t count) { void* v = nullptr; if (cudaMalloc(&v, (count ? count : 1) * sizeof(T)) != cudaSuccess) { p = nullptr; return false; } ptrs.push_back(v); p = (T*)v; return true; }
+struct Tmp {                          // scratch of one build: pool blocks, given back once the stream has drained
+    std::vector<std::pair<void*, size_t>> ptrs; int device = 0; cudaStream_t st = nullptr;
+    ~Tmp() { if (!ptrs.empty()) cudaStreamSynchronize(st); for (auto& b : ptrs) pool_give(device, b.second, b.first); }
+    template <class T> bool get(T*& p, size_t count)
+    {
+        void* v = nullptr; const size_t bytes = (count ? count : 1) * sizeof(T);
+        if (pool_alloc(device, bytes, &v) != cudaSuccess) { p = nullptr; return false; }
+        ptrs.emplace_back(v, bytes); p = (T*)v; return true;
+    }
 };
 
 inline double now_ms()
@@ -315,7 +320,8 @@ inline int bits_for(uint64_t v) { int b = 0; while (v) { ++b; v >>= 1; } return 
 #define GB_CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { err = std::string(#x) + ": " + cudaGetErrorString(e_); return false; } } while (0)
 
 bool build_mesh_gpu(const MeshSource& src, int64_t n_tri, uint64_t seed, int shape_id,
-                    cudaStream_t st, std::vector<void*>& allocs, size_t& bytes, GpuMeshBuild& out, std::string& err, uint64_t* launches)
+                    cudaStream_t st, std::vector<void*>& allocs, std::unordered_map<void*, size_t>& alloc_bytes, size_t& bytes, GpuMeshBuild& out,
+                    std::string& err, uint64_t* launches)
 {
     out = GpuMeshBuild();
     if (n_tri <= 0) { out.mesh.ref_root = -1; return true; }
@@ -325,9 +331,14 @@ bool build_mesh_gpu(const MeshSource& src, int64_t n_tri, uint64_t seed, int sha
     TreeShape ts; tree_shape_fill(ts, (uint32_t)n);
     const size_t n_nodes = ts.nodes[0][0], n_leaves = ts.bottoms[0][0];
 
-    Tmp tmp;
+    int device = 0; cudaGetDevice(&device);
+    Tmp tmp; tmp.device = device; tmp.st = st;
     const size_t allocs_at_entry = allocs.size(); const size_t bytes_at_entry = bytes;
-    auto drop_results = [&]() { while (allocs.size() > allocs_at_entry) { cudaFree(allocs.back()); allocs.pop_back(); } bytes = bytes_at_entry; };
+    auto drop_results = [&]() {
+        cudaStreamSynchronize(st);
+        while (allocs.size() > allocs_at_entry) { void* p = allocs.back(); pool_give(device, alloc_bytes[p], p); alloc_bytes.erase(p); allocs.pop_back(); }
+        bytes = bytes_at_entry;
+    };
     float *d_pos, *d_nrm, *d_uv; float4 *d_tmin, *d_tmax; unsigned int *d_order[2]; unsigned long long* d_keys[2];
     uint8_t* d_axis; int* d_flags; unsigned int* d_idx = nullptr;
     const size_t n_in = src.indexed ? (size_t)src.n_vert : n * 3;        // vertices that cross PCIe
@@ -337,7 +348,11 @@ bool build_mesh_gpu(const MeshSource& src, int64_t n_tri, uint64_t seed, int sha
         !tmp.get(d_axis, n_nodes) || !tmp.get(d_flags, 16)) { err = "out of device memory (BVH build scratch)"; return false; }
     // results (owned by the scene)
     float4 *d_tris = nullptr, *d_attrs = nullptr, *d_ref = nullptr, *d_leaves = nullptr, *d_fast = nullptr;
-    auto keep = [&](float4*& p, size_t count) { void* v = nullptr; if (cudaMalloc(&v, (count ? count : 1) * sizeof(float4)) != cudaSuccess) return false; allocs.push_back(v); bytes += count * sizeof(float4); p = (float4*)v; return true; };
+    auto keep = [&](float4*& p, size_t count) {
+        void* v = nullptr; const size_t nb = (count ? count : 1) * sizeof(float4);
+        if (pool_alloc(device, nb, &v) != cudaSuccess) return false;
+        allocs.push_back(v); alloc_bytes[v] = nb; bytes += count * sizeof(float4); p = (float4*)v; return true;
+    };
     if (!keep(d_tris, n * 3) || !keep(d_attrs, n * 4) || !keep(d_ref, n_nodes * 2) || !keep(d_leaves, n_leaves * 8) || !keep(d_fast, n_leaves > 1 ? (n_leaves - 1) * 4 : 0)) { err = "out of device memory (mesh arrays)"; return false; }
 
     GB_CK(cudaMemcpyAsync(d_pos, src.pos, n_in * 3 * sizeof(float), cudaMemcpyHostToDevice, st));

@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "hrt_types.h"
@@ -31,10 +32,18 @@ struct MeshSource {
     bool indexed = false;
 };
 
+// Size-keyed cache of device blocks shared by the uploads of hrt_scene_commit and the device builder (hrt_api.cu): blocks of a
+// destroyed scene and the builder's scratch are kept (bounded; hrt_trim frees them) for the next build of this process, so a host
+// that rebuilds its scene every frame neither pays cudaMalloc nor the device-wide synchronisation of cudaFree while another scene
+// of the process is rendering.  A block is only given back once no stream uses it any more.
+cudaError_t pool_alloc(int device, size_t bytes, void** p);   // a cached block of exactly this size, else cudaMalloc
+void pool_give(int device, size_t bytes, void* p);            // keeps the block, or cudaFree when the cache is full
+
 // Uploads the mesh source and builds every per-mesh array on the device (an indexed source is gathered there, so only
-// the compact buffers cross PCIe).  Result allocations are appended to `allocs` (owned by the scene).  Returns false
+// the compact buffers cross PCIe).  Result allocations are appended to `allocs`, their sizes to `alloc_bytes` (owned by the scene; pool blocks).  Returns false
 // with `err` set on a CUDA failure.
 bool build_mesh_gpu(const MeshSource& src, int64_t n_tri, uint64_t seed, int shape_id,
-                    cudaStream_t st, std::vector<void*>& allocs, size_t& bytes, GpuMeshBuild& out, std::string& err, uint64_t* launches);
+                    cudaStream_t st, std::vector<void*>& allocs, std::unordered_map<void*, size_t>& alloc_bytes, size_t& bytes, GpuMeshBuild& out,
+                    std::string& err, uint64_t* launches);
 
 } // namespace hrt

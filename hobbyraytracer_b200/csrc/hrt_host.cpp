@@ -740,6 +740,15 @@ std::string flatten(HostScene& s, int bvh_mode, uint64_t seed)
         for (size_t k = 0; k < obmin.size(); ++k) { obmin[k] = std::nextafter(obmin[k], -std::numeric_limits<float>::infinity()); obmax[k] = std::nextafter(obmax[k], std::numeric_limits<float>::infinity()); }
         build_fast_bvh(obmin, obmax, s.tlas, 1);
         build_wide(s.tlas, s.tlas_wide);
+        // top-level leaves of meshes that get entered carry WIDE_MESH_BIT (hrt_wide.cuh: the mesh-entry phase is told apart without a load)
+        auto mark = [&](int32_t c) -> int32_t {
+            if (c >= 0) return c;
+            const DObject& ob = s.d_objects[(size_t)(~c)];
+            return (ob.kind == SHAPE_MESH && !ob.medium) ? (int32_t)~((uint32_t)(~c) | (1u << 30)) : c;
+        };
+        for (WNode& n : s.tlas_wide.nodes)
+            for (int k = 0; k < 8; ++k) if ((n.meta >> (24 + k)) & 1u) n.child[k] = mark(n.child[k]);
+        s.tlas_wide.root = mark(s.tlas_wide.root);
         s.has_bounds = true;
         for (int a = 0; a < 3; ++a) { s.bounds_lo[a] = 3.0e38f; s.bounds_hi[a] = -3.0e38f; }
         for (size_t k = 0; k < obmin.size(); ++k) {

@@ -28,6 +28,9 @@ constexpr int WIDE_STACK = 32;                        // stack entries per lane 
 constexpr float WIDE_WIDEN = 9.5367431640625e-7f;     // 2^-20, relative to |(p - o) / d| + |grid extent / d| (see wide_hits)
 constexpr int HIT_PENDING = 8;                        // Hit::flags: pass 1 could not decide; Hit::t carries the cull bound
 constexpr int PEND_BAD = 16, PEND_SHEAR = 32;         // Hit::flags of a pending entry: arguments of trace_resolve
+constexpr uint32_t WIDE_MESH_BIT = 1u << 30;          // top-level leaf ~(entry | WIDE_MESH_BIT): the entry is a mesh that gets ENTERED (no medium),
+                                                      // so a warp can tell the lanes that wait for a mesh entry from those that wait for
+                                                      // a sphere / rect / box / medium test without a load (set by flatten(), hrt_host.cpp)
 
 struct __align__(32) W32 { uint32_t w[8]; };
 
@@ -174,16 +177,23 @@ HRT_HD int wide_fls(uint32_t m)
     return 31 - __builtin_clz(m);
 #endif
 }
-template <class St> HRT_HD void wide_pop(WideLane& L, const DScene& s, St& st)
+// What every step ends with: the lane's next node or leaf.  `group` is the group a node step just produced (its nearest child is
+// taken, the others are stacked) or 0 (the nearest remaining child of the group on top of the stack).  ONE copy of this code per
+// kernel, run after the phases of a round for all the lanes that took a step (r2o profile: inlined at the end of each step it
+// ran with 4.8 of 32 lanes and made a third of the hot code).
+template <class St> HRT_HD void wide_pop(WideLane& L, const DScene& s, St& st, uint32_t group)
 {
     for (;;) {
-        if (st.empty() || L.b.bad) { L.live = false; return; }
-        const uint32_t v = (uint32_t)st.top();
-        if (v == (uint32_t)WALK_MARK) { st.drop(); wide_enter_top(L, s); continue; }     // the mesh is done: back to the world ray
+        uint32_t v = group;
+        if (v == 0u) {
+            if (st.empty() || L.b.bad) { L.live = false; return; }
+            v = (uint32_t)st.top(); st.drop();
+            if (v == (uint32_t)WALK_MARK) { wide_enter_top(L, s); continue; }            // the mesh is done: back to the world ray
+        }
         uint32_t mp = v & 0xffu; const uint32_t node = v >> 8;
         const int k = wide_fls(mp);
         mp &= ~(1u << k);
-        if (mp) st.set_top((int)((node << 8) | mp)); else st.drop();
+        if (mp && !st.push((int)((node << 8) | mp))) { L.b.bad = 1; L.live = false; return; }
         L.cur = wide_ld_child(L.nodes, node, (uint32_t)k ^ L.q.oct);
         return;
     }
@@ -212,20 +222,17 @@ HRT_HD bool wide_begin(WideLane& L, const DScene& s, const Ray& r, float t_min, 
     return true;
 }
 
-// ---- node step: tests the eight children of node L.cur, continues with the nearest one (octant order), stacks the others
-template <class St> HRT_HD void wide_node_step(WideLane& L, const DScene& s, St& st)
+// ---- node step: tests the eight children of node L.cur; returns the group (node << 8 | children hit, in walking order: the highest
+// bit is the nearest octant) for wide_pop, 0 when the ray misses them all
+HRT_HD uint32_t wide_node_step(WideLane& L)
 {
     const uint32_t node = (uint32_t)L.cur;
     const char* N = (const char*)(L.nodes + (size_t)node);
     const W32 c0 = wide_ld32(N), c1 = wide_ld32(N + 32);
     wide_prefetch(N + 64);
     const float t_lo = fminf(L.t_min, 0.0f);                                    // ITriangle::hit ignores t_min but only reports t > 0
-    uint32_t mp = wide_xor_bits(wide_hits(c0, c1, L.q, t_lo, L.bnd0), L.q.oct);   // walking order: the highest bit is the nearest octant
-    if (mp == 0) { wide_pop(L, s, st); return; }
-    const int k = wide_fls(mp);
-    mp &= ~(1u << k);
-    if (mp && !st.push((int)((node << 8) | mp))) { L.b.bad = 1; L.live = false; return; }
-    L.cur = wide_ld_child(L.nodes, node, (uint32_t)k ^ L.q.oct);
+    const uint32_t mp = wide_xor_bits(wide_hits(c0, c1, L.q, t_lo, L.bnd0), L.q.oct);
+    return mp ? ((node << 8) | mp) : 0u;
 }
 
 // itriangle_t<3> (hrt_trace.cuh) without early exits: the same operations in the same order on every lane, the verdict formed at
@@ -254,7 +261,7 @@ HRT_HD bool wide_itriangle(const float4& P0, const float4& P1, const float4& P2,
 
 // ---- triangle leaf: the 1-2 triangles of a bottom node of the reference topology, exact ITriangle arithmetic; the reference's own
 // slab test of the node box only for a triangle that accepted (world_walk has the reasoning)
-template <class St> HRT_HD void wide_leaf_step(WideLane& L, const DScene& s, St& st)
+HRT_HD void wide_leaf_step(WideLane& L)
 {
     const uint32_t leaf = (uint32_t)(~L.cur);
     const char* R = (const char*)(L.leaves + 8 * (size_t)leaf);
@@ -276,52 +283,50 @@ template <class St> HRT_HD void wide_leaf_step(WideLane& L, const DScene& s, St&
             wide_set_bound(L);
         }
     }
-    wide_pop(L, s, st);
 }
 
-// ---- world-list entry: a mesh is entered (local ray, marker on the stack), anything else is tested on the spot
-template <class St> HRT_HD void wide_object_step(WideLane& L, const DScene& s, St& st, const RngKey& key, uint32_t bounce)
+// ---- world-list entry that is a mesh (WIDE_MESH_BIT): entered with the local ray, a marker goes on the stack.  Returns true when the
+// mesh was NOT entered (empty mesh, or a ray pass 2 has to take: L.b.bad / L.b.shear) and the lane pops instead.
+template <class St> HRT_HD bool wide_mesh_step(WideLane& L, const DScene& s, St& st)
 {
-    // (one entry per call: taking a lane's next entries in the same call - a Cornell-box ray holds three in a row - was slower,
-    // teapot_scene 1612 -> 1496 Mrays/s, and unrolled it outgrew the instruction cache: 931, profiles/README.md r2h / r2i)
-    {
-        const int i = ~L.cur;
-        const DObject& ob = s.objects[i];
-        if (ob.kind == SHAPE_MESH && !ob.medium) {
-            const DMesh& m = s.meshes[ob.mesh];
-            if (m.ref_root >= 0) {
-                Ray lr = L.r; V3 id = L.rid; bool ok = true;
-                if (ob.xf_count > 0) {
-                    lr = to_local(s, ob, L.r);
-                    id = v3(1.0f / lr.d.x, 1.0f / lr.d.y, 1.0f / lr.d.z);
-                    ok = recip_ok(id) && hrt_finite(lr.o.x) && hrt_finite(lr.o.y) && hrt_finite(lr.o.z);
-                }
-                const int kz = tri_kz(lr.o);
-                if (!ok) L.b.bad = 1;
-                else if (!shear_ok(lr, kz)) L.b.shear = 1;                      // pass 2 collects every hit along this ray
-                else if (!st.push(WALK_MARK)) L.b.bad = 1;
-                else {
-                    L.q = wide_ray(lr.o, lr.d, id);
-                    L.nodes = m.wide_nodes; L.leaves = m.fast_leaves; L.prim_base = m.prim_base; L.obj = i;
-                    L.ld = lr.d; L.tq = tri_ray<3>(lr, kz);
-                    wide_set_bound(L);
-                    L.cur = m.wide_root;
-                    return;
-                }
-            }
-        } else {
-            float t = 0.0f; uint32_t prim = ob.prim_base; bool hit;
-            const float bound = cull_bound(L.b);
-            if (!ob.medium && ob.xf_count == 0 && ob.kind == SHAPE_SPHERE) hit = sphere_t(ob.f, L.r, L.t_min, bound, t);    // the common entries in line
-            else if (!ob.medium && ob.xf_count == 0 && ob.kind == SHAPE_RECT) { float a, b; hit = rect_t(ob.axis, ob.f[0], ob.f[1], ob.f[2], ob.f[3], ob.f[4], L.r, L.t_min, bound, t, a, b); }
-            else {
-                const Ray wr = L.r;                                             // a copy: hit_object_ref is out of line
-                hit = hit_object_ref(s, i, wr, L.t_min, bound, t, prim, key, bounce);
-            }
-            if (hit) { consider(L.b, t, t, prim, i); wide_set_bound(L); }
-        }
-        wide_pop(L, s, st);
+    const int i = (int)((uint32_t)(~L.cur) & ~WIDE_MESH_BIT);
+    const DObject& ob = s.objects[i];
+    const DMesh& m = s.meshes[ob.mesh];
+    if (m.ref_root < 0) return true;
+    Ray lr = L.r; V3 id = L.rid; bool ok = true;
+    if (ob.xf_count > 0) {
+        lr = to_local(s, ob, L.r);
+        id = v3(1.0f / lr.d.x, 1.0f / lr.d.y, 1.0f / lr.d.z);
+        ok = recip_ok(id) && hrt_finite(lr.o.x) && hrt_finite(lr.o.y) && hrt_finite(lr.o.z);
     }
+    const int kz = tri_kz(lr.o);
+    if (!ok) { L.b.bad = 1; return true; }
+    if (!shear_ok(lr, kz)) { L.b.shear = 1; return true; }                      // pass 2 collects every hit along this ray
+    if (!st.push(WALK_MARK)) { L.b.bad = 1; return true; }
+    L.q = wide_ray(lr.o, lr.d, id);
+    L.nodes = m.wide_nodes; L.leaves = m.fast_leaves; L.prim_base = m.prim_base; L.obj = i;
+    L.ld = lr.d; L.tq = tri_ray<3>(lr, kz);
+    wide_set_bound(L);
+    L.cur = m.wide_root;
+    return false;
+}
+
+// ---- any other world-list entry (sphere, rect, box, medium ...): tested on the spot
+// (one entry per call: taking a lane's next entries in the same call - a Cornell-box ray holds three in a row - was slower,
+// teapot_scene 1612 -> 1496 Mrays/s, and unrolled it outgrew the instruction cache: 931, profiles/README.md r2h / r2i)
+HRT_HD void wide_object_step(WideLane& L, const DScene& s, const RngKey& key, uint32_t bounce)
+{
+    const int i = (int)((uint32_t)(~L.cur) & ~WIDE_MESH_BIT);
+    const DObject& ob = s.objects[i];
+    float t = 0.0f; uint32_t prim = ob.prim_base; bool hit;
+    const float bound = cull_bound(L.b);
+    if (!ob.medium && ob.xf_count == 0 && ob.kind == SHAPE_SPHERE) hit = sphere_t(ob.f, L.r, L.t_min, bound, t);    // the common entries in line
+    else if (!ob.medium && ob.xf_count == 0 && ob.kind == SHAPE_RECT) { float a, b; hit = rect_t(ob.axis, ob.f[0], ob.f[1], ob.f[2], ob.f[3], ob.f[4], L.r, L.t_min, bound, t, a, b); }
+    else {
+        const Ray wr = L.r;                                             // a copy: hit_object_ref is out of line
+        hit = hit_object_ref(s, i, wr, L.t_min, bound, t, prim, key, bounce);
+    }
+    if (hit) { consider(L.b, t, t, prim, i); wide_set_bound(L); }
 }
 
 // what pass 1 found, as a hit record: final, or pending (the caller queues the ray for trace_resolve)
@@ -357,9 +362,12 @@ HRT_HDN inline Hit wide_trace_scalar(const DScene& s, const Ray& r, float t_min,
         WideArrayStack st;
         while (L.live) {
             if (steps) ++*steps;
-            if (L.cur >= 0) wide_node_step(L, s, st);
-            else if (L.obj >= 0) wide_leaf_step(L, s, st);
-            else wide_object_step(L, s, st, key, bounce);
+            uint32_t group = 0u; bool pop = true;
+            if (L.cur >= 0) group = wide_node_step(L);
+            else if (L.obj >= 0) wide_leaf_step(L);
+            else if ((uint32_t)(~L.cur) & WIDE_MESH_BIT) pop = wide_mesh_step(L, s, st);
+            else wide_object_step(L, s, key, bounce);
+            if (pop) wide_pop(L, s, st, group);
         }
     }
     h = wide_result(L);
@@ -387,22 +395,29 @@ template <int THREADS> struct WideSmemStack {
     __device__ __forceinline__ bool empty() const { return sp == 0; }
 };
 
-// One round of the warp: every lane that is walking waits for a node step, a triangle leaf or a world-list entry; the phases
-// that enough lanes wait for run, the others wait for the next round.  Must be called by all 32 lanes; returns false when no
-// lane is walking.
+// One round of the warp: every lane that is walking waits for a node step, a triangle leaf, a mesh entry or another world-list
+// entry; the phases that enough lanes wait for run, the others wait for the next round; the lanes that took a step then fetch
+// their next node together (wide_pop).  Must be called by all 32 lanes; returns false when no lane is walking.
 template <class St>
 __device__ __forceinline__ bool wide_round(WideLane& L, const DScene& s, St& st, const RngKey& key, uint32_t bounce)
 {
+    const bool top_leaf = L.live && L.cur < 0 && L.obj < 0;
+    const bool is_mesh = ((uint32_t)(~L.cur) & WIDE_MESH_BIT) != 0u;
     const bool w_in = L.live && L.cur >= 0;
     const bool w_tl = L.live && L.cur < 0 && L.obj >= 0;
-    const bool w_ob = L.live && L.cur < 0 && L.obj < 0;
-    const int n_in = __popc(__ballot_sync(0xffffffffu, w_in)), n_tl = __popc(__ballot_sync(0xffffffffu, w_tl)), n_ob = __popc(__ballot_sync(0xffffffffu, w_ob));
-    const int most = max(n_in, max(n_tl, n_ob));
+    const bool w_me = top_leaf && is_mesh;
+    const bool w_ob = top_leaf && !is_mesh;
+    const int n_in = __popc(__ballot_sync(0xffffffffu, w_in)), n_tl = __popc(__ballot_sync(0xffffffffu, w_tl));
+    const int n_me = __popc(__ballot_sync(0xffffffffu, w_me)), n_ob = __popc(__ballot_sync(0xffffffffu, w_ob));
+    const int most = max(max(n_in, n_tl), max(n_me, n_ob));
     if (most == 0) return false;
     const int need = most < HRT_WIDE_PHASE_MIN ? most : HRT_WIDE_PHASE_MIN;
-    if (n_in >= need) { if (w_in) wide_node_step(L, s, st); }
-    if (n_tl >= need) { if (w_tl) wide_leaf_step(L, s, st); }
-    if (n_ob >= need) { if (w_ob) wide_object_step(L, s, st, key, bounce); }
+    uint32_t group = 0u; bool pop = false;
+    if (n_in >= need) { if (w_in) { group = wide_node_step(L); pop = true; } }
+    if (n_tl >= need) { if (w_tl) { wide_leaf_step(L); pop = true; } }
+    if (n_me >= need) { if (w_me) pop = wide_mesh_step(L, s, st); }
+    if (n_ob >= need) { if (w_ob) { wide_object_step(L, s, key, bounce); pop = true; } }
+    if (pop) wide_pop(L, s, st, group);
     return true;
 }
 #endif

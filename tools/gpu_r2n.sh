@@ -16,5 +16,10 @@ run $C5 > $O/plain_c5.log 2>&1 && run $NCU -k regex:'k_wave2_trace|k_wide_second
 for r in c1 rb c5; do
   [ -f $O/r2n_$r.ncu-rep ] && ncu -i $O/r2n_$r.ncu-rep --page raw --csv > $O/r2n_${r}_raw.csv 2>/dev/null
 done
+# SASS view of the first captured launch of the two walk kernels (per-instruction executed counts / lanes), then drop the reports:
+# gpurun_out/ travels back only below 64 MiB
+ncu -i $O/r2n_c1.ncu-rep --page source --csv --kernel-name regex:k_wide_secondary --launch-count 1 > $O/r2n_c1_wsec_source.csv 2>/dev/null
+ncu -i $O/r2n_rb.ncu-rep --page source --csv --kernel-name regex:k_trace_batch --launch-count 1 > $O/r2n_rb_source.csv 2>/dev/null
+rm -f $O/*.ncu-rep
 ls -la $O | head -40
 bash tools/gpu_sanitize.sh memcheck

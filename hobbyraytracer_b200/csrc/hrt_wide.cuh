@@ -181,10 +181,11 @@ HRT_HD int wide_fls(uint32_t m)
 // taken, the others are stacked) or 0 (the nearest remaining child of the group on top of the stack).  ONE copy of this code per
 // kernel, run after the phases of a round for all the lanes that took a step (r2o profile: inlined at the end of each step it
 // ran with 4.8 of 32 lanes and made a third of the hot code).
-template <class St> HRT_HD void wide_pop(WideLane& L, const DScene& s, St& st, uint32_t group)
+// The group travels in L.cur (dead between a step and the pop): steps leave it there, 0 for "none".
+template <class St> HRT_HD void wide_pop(WideLane& L, const DScene& s, St& st)
 {
     for (;;) {
-        uint32_t v = group;
+        uint32_t v = (uint32_t)L.cur; L.cur = 0;
         if (v == 0u) {
             if (st.empty() || L.b.bad) { L.live = false; return; }
             v = (uint32_t)st.top(); st.drop();
@@ -223,8 +224,8 @@ HRT_HD bool wide_begin(WideLane& L, const DScene& s, const Ray& r, float t_min, 
 }
 
 // ---- node step: tests the eight children of node L.cur; returns the group (node << 8 | children hit, in walking order: the highest
-// bit is the nearest octant) for wide_pop, 0 when the ray misses them all
-HRT_HD uint32_t wide_node_step(WideLane& L)
+// bit is the nearest octant) for wide_pop in L.cur, 0 when the ray misses them all
+HRT_HD void wide_node_step(WideLane& L)
 {
     const uint32_t node = (uint32_t)L.cur;
     const char* N = (const char*)(L.nodes + (size_t)node);
@@ -232,7 +233,7 @@ HRT_HD uint32_t wide_node_step(WideLane& L)
     wide_prefetch(N + 64);
     const float t_lo = fminf(L.t_min, 0.0f);                                    // ITriangle::hit ignores t_min but only reports t > 0
     const uint32_t mp = wide_xor_bits(wide_hits(c0, c1, L.q, t_lo, L.bnd0), L.q.oct);
-    return mp ? ((node << 8) | mp) : 0u;
+    L.cur = mp ? (int)((node << 8) | mp) : 0;
 }
 
 // itriangle_t<3> (hrt_trace.cuh) without early exits: the same operations in the same order on every lane, the verdict formed at
@@ -283,6 +284,7 @@ HRT_HD void wide_leaf_step(WideLane& L)
             wide_set_bound(L);
         }
     }
+    L.cur = 0;
 }
 
 // ---- world-list entry that is a mesh (WIDE_MESH_BIT): entered with the local ray, a marker goes on the stack.  Returns true when the
@@ -292,6 +294,7 @@ template <class St> HRT_HD bool wide_mesh_step(WideLane& L, const DScene& s, St&
     const int i = (int)((uint32_t)(~L.cur) & ~WIDE_MESH_BIT);
     const DObject& ob = s.objects[i];
     const DMesh& m = s.meshes[ob.mesh];
+    L.cur = 0;
     if (m.ref_root < 0) return true;
     Ray lr = L.r; V3 id = L.rid; bool ok = true;
     if (ob.xf_count > 0) {
@@ -327,6 +330,7 @@ HRT_HD void wide_object_step(WideLane& L, const DScene& s, const RngKey& key, ui
         hit = hit_object_ref(s, i, wr, L.t_min, bound, t, prim, key, bounce);
     }
     if (hit) { consider(L.b, t, t, prim, i); wide_set_bound(L); }
+    L.cur = 0;
 }
 
 // what pass 1 found, as a hit record: final, or pending (the caller queues the ray for trace_resolve)
@@ -362,12 +366,12 @@ HRT_HDN inline Hit wide_trace_scalar(const DScene& s, const Ray& r, float t_min,
         WideArrayStack st;
         while (L.live) {
             if (steps) ++*steps;
-            uint32_t group = 0u; bool pop = true;
-            if (L.cur >= 0) group = wide_node_step(L);
+            bool pop = true;
+            if (L.cur >= 0) wide_node_step(L);
             else if (L.obj >= 0) wide_leaf_step(L);
             else if ((uint32_t)(~L.cur) & WIDE_MESH_BIT) pop = wide_mesh_step(L, s, st);
             else wide_object_step(L, s, key, bounce);
-            if (pop) wide_pop(L, s, st, group);
+            if (pop) wide_pop(L, s, st);
         }
     }
     h = wide_result(L);
@@ -412,12 +416,12 @@ __device__ __forceinline__ bool wide_round(WideLane& L, const DScene& s, St& st,
     const int most = max(max(n_in, n_tl), max(n_me, n_ob));
     if (most == 0) return false;
     const int need = most < HRT_WIDE_PHASE_MIN ? most : HRT_WIDE_PHASE_MIN;
-    uint32_t group = 0u; bool pop = false;
-    if (n_in >= need) { if (w_in) { group = wide_node_step(L); pop = true; } }
+    bool pop = false;
+    if (n_in >= need) { if (w_in) { wide_node_step(L); pop = true; } }
     if (n_tl >= need) { if (w_tl) { wide_leaf_step(L); pop = true; } }
     if (n_me >= need) { if (w_me) pop = wide_mesh_step(L, s, st); }
     if (n_ob >= need) { if (w_ob) { wide_object_step(L, s, key, bounce); pop = true; } }
-    if (pop) wide_pop(L, s, st, group);
+    if (pop) wide_pop(L, s, st);
     return true;
 }
 #endif

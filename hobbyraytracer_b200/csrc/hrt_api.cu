@@ -323,13 +323,22 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
         const bool have_prior = s->have_secondary_prior;
         bool secondary_heavy = have_prior ? s->last_secondary_heavy : g_last_secondary_heavy.load();
         int chunk_len[CTL_RING] = {0}, chunk_end_it[CTL_RING] = {0};
+        bool camera_done = false;
         auto retire = [&](int chunk) -> int {               // waits for the chunk, adds its kernel times, looks at its snapshot
             cudaEvent_t* ev = s->events.data() + (size_t)EV_PER_CHUNK * (size_t)(chunk % CTL_RING);
             CK(cudaEventSynchronize(ev[2 * CHUNK + 1]));
             float ms = 0;
+            static const bool dbg_iter = getenv("HRT_DEBUG_ITER") != nullptr;     // per-pass timeline on stderr (tuning)
             for (int k = 0; k < chunk_len[chunk % CTL_RING]; ++k) {
+                float ms2 = 0;
                 CK(cudaEventElapsedTime(&ms, ev[2 * k], ev[2 * k + 1])); s->stats.ms_trace += ms;
-                CK(cudaEventElapsedTime(&ms, ev[2 * k + 1], ev[2 * k + 2])); s->stats.ms_shade += ms;
+                CK(cudaEventElapsedTime(&ms2, ev[2 * k + 1], ev[2 * k + 2])); s->stats.ms_shade += ms2;
+                if (dbg_iter) fprintf(stderr, "[hrt] pass %3d: trace %8.3f ms  shade %7.3f ms\n", chunk_end_it[chunk % CTL_RING] - chunk_len[chunk % CTL_RING] + k, ms, ms2);
+            }
+            if (dbg_iter) {
+                const WaveCtl& d = s->h_ctl[chunk % CTL_RING];
+                fprintf(stderr, "[hrt]   after pass %d: claims %llu / %llu, queue entries %u / %u, secondary rays so far %llu, heavy %d\n", chunk_end_it[chunk % CTL_RING] - 1,
+                        d.next_path < d.total_paths ? d.next_path : d.total_paths, d.total_paths, d.n_front[0], d.n_front[1], d.rays, (int)secondary_heavy);
             }
             const WaveCtl& c = s->h_ctl[chunk % CTL_RING];
             const int o = chunk_end_it[chunk % CTL_RING] & 1; // queue the last shade pass of the chunk filled
@@ -340,13 +349,21 @@ int render_into(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p,
                 s->last_secondary_heavy = secondary_heavy; s->have_secondary_prior = true;
                 g_last_secondary_heavy.store(secondary_heavy);
             }
+            if (handed == c.total_paths) camera_done = true;     // the tail: shorter chunks, the host looks more often
             if (v1 ? (c.n_front[o] == 0 && handed == c.base[o] && handed == c.total_paths) : (c.n_front[o] == 0 && handed == c.total_paths)) done = true;
             return 0;
         };
         while (!done) {
             if (issued - retired >= CTL_RING - 1 || (issued == 1 && !have_prior)) { rc = retire(retired++); if (rc < 0) return rc; if (done) break; }
+            // chunks that have finished meanwhile are looked at right away (no wait): in the tail of a render, where a pass takes 20-100 us, the
+            // host then sees the empty queue one chunk late instead of three (r2t timeline: 16 empty passes = 0.3 ms of a 31 ms step)
+            while (!done && retired < issued) {
+                if (cudaEventQuery(s->events[(size_t)EV_PER_CHUNK * (size_t)(retired % CTL_RING) + 2 * CHUNK + 1]) != cudaSuccess) { (void)cudaGetLastError(); break; }   // not ready (a real failure is sticky and shows at the next call)
+                rc = retire(retired++); if (rc < 0) return rc;
+            }
+            if (done) break;
             cudaEvent_t* ev = s->events.data() + (size_t)EV_PER_CHUNK * (size_t)(issued % CTL_RING);
-            const int len = (issued == 0 && !have_prior) ? 2 : CHUNK;
+            const int len = (issued == 0 && !have_prior) ? 2 : (camera_done ? 4 : CHUNK);
             chunk_len[issued % CTL_RING] = len; chunk_end_it[issued % CTL_RING] = it + len;
             for (int k = 0; k < len; ++k, ++it) {
                 CK(cudaEventRecord(ev[2 * k], st));

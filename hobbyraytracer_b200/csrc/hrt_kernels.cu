@@ -100,8 +100,11 @@ __global__ void __launch_bounds__(BLOCK, HRT_BATCH_MIN_BLOCKS) k_trace_batch(DSc
 // pass 2 of the rays k_trace_batch left pending
 __global__ void __launch_bounds__(BLOCK) k_resolve_batch(DScene s, const float4* __restrict__ rays, Hit* __restrict__ hits, uint64_t seed, PendList pend)
 {
+    // entry k goes to warp k mod (number of warps): a short list gives every ray a warp of its own - the ordered pass 2 of 32 unrelated rays
+    // in one warp runs every lane's loop to the longest one with both sides of every branch
     const unsigned int n = *pend.count;
-    for (unsigned int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+    const unsigned int nw = gridDim.x * (blockDim.x >> 5), wid = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
+    for (unsigned int k = wid + nw * lane; k < n; k += nw * 32u) {
         const unsigned int i = pend.idx[k];
         float4 a = __ldg(rays + 2 * (size_t)i), b = __ldg(rays + 2 * (size_t)i + 1);
         Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
@@ -736,7 +739,8 @@ __global__ void __launch_bounds__(BLOCK) k_wave3_resolve(DScene s, WaveJob j, in
     WaveCtl* c = j.ctl;
     const unsigned int n = c->pend_count;
     const float4* __restrict__ rays = j.rays[q];
-    for (unsigned int k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+    const unsigned int nw = gridDim.x * (blockDim.x >> 5), wid = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
+    for (unsigned int k = wid + nw * lane; k < n; k += nw * 32u) {                    // one warp per entry while the list is short (k_resolve_batch)
         const unsigned int e = j.pend[k];
         const float4 a = rays[2 * (size_t)e], b = rays[2 * (size_t)e + 1];
         Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
@@ -791,7 +795,7 @@ void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit*
     PendList pend; pend.idx = d_pend_idx; pend.count = d_pend_count;
     if (!s.wide || getenv("HRT_NO_WIDE")) { k_trace_batch_plain<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed); *launches += 1; return; }
     k_trace_batch<<<grid_for(n, sm_count, HRT_BATCH_MIN_BLOCKS), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed, d_counter, pend);
-    k_resolve_batch<<<sm_count * 2, BLOCK, 0, st>>>(s, d_rays, d_hits, seed, pend); *launches += 2;
+    k_resolve_batch<<<sm_count * 8, BLOCK, 0, st>>>(s, d_rays, d_hits, seed, pend); *launches += 2;
 }
 // ---- hrt_trace_batch_static: the ray batch without any allocation -------------------------------------------------------------------
 // The scratch of k_trace_batch / k_resolve_batch / k_split_hits (hit records, hand-out counter, pending list) lives in one file-scope
@@ -918,7 +922,7 @@ void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, i
         if (lens) k_wave2_trace<4, true, false><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, q, wsec);
         else k_wave2_trace<4, false, false><<<wave2_trace_blocks(j.capacity, sm_count, 4), BLOCK, 0, st>>>(s, j, cam, q, wsec);
     }
-    k_wave3_resolve<<<sm_count * 2, BLOCK, 0, st>>>(s, j, q);
+    k_wave3_resolve<<<sm_count * 8, BLOCK, 0, st>>>(s, j, q);
     *launches += 2;
 }
 void launch_wave2_shade(const DScene& s, const WaveJob& j, int it, int sm_count, cudaStream_t st, uint64_t* launches)

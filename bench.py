@@ -329,10 +329,12 @@ def run_own(args):
         b_alg, n_prims = alg_bytes_per_ray(sd)
         rank_rays = float(st.rays)
         ach = rank_rays * b_alg / (st.ms_trace * 1e-3) / 1e9 if st.ms_trace > 0 else None
-        traffic = traffic_src = None
+        traffic = traffic_src = traffic_ms = traffic_kernel = None
         try:                                    # dram__bytes of one launch of the dominant kernel from an ncu --set full capture (not measured in this run)
             tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-            traffic = tj.get(args.workload); traffic_src = tj.get("source") if traffic is not None else None
+            ent = tj.get(args.workload)
+            if isinstance(ent, dict):
+                traffic, traffic_src, traffic_ms, traffic_kernel = ent.get("bytes"), ent.get("source"), ent.get("launch_ms"), ent.get("kernel")
         except Exception:
             pass
         line = {"metric": "Mrays/s", "value": rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -345,9 +347,10 @@ def run_own(args):
                         "d2h_bytes_per_step": npix * 15, "steps": e2e_steps, "includes": "scene build + BVH build + upload, render, float film + 8-bit image read-back; steps pipelined two deep (a builder thread commits the scene of step k + 1 while step k renders)"},
                 "gpu_launches": int(launches), "commit_s": t_commit, "build_ms": st.ms_build, "replayed_fraction": float(st.retraced) / max(float(st.rays), 1.0), "ref_walk_rays": int(st.prim_tests),
                 "kernel_ms": {"trace": st.ms_trace, "shade": st.ms_shade, "other": st.ms_other, "total": st.ms_total, "note": "rank 0, CUDA events inside the timed region"},
-                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": (ach / peak) if ach else None, "traffic": traffic, "traffic_source": traffic_src,
-                             "kernel": "k_wave_trace" if args.pipeline == "v1" else "k_wave2_trace", "alg_bytes_per_ray": b_alg, "trace_launches": int(st.launches) // 2, "peak_source": peak_src,
-                             "note": "achieved = rays x B_alg / device time of the traversal kernel (CUDA events); the scene is L1/L2 resident and camera paths live in registers, so DRAM traffic is far below the algorithmic bytes: the kernel is issue/latency bound, see DESIGN.md"},
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": (ach / peak) if ach else None, "traffic": traffic, "traffic_source": traffic_src, "traffic_launch_ms": traffic_ms,
+                             "traffic_gbs": (traffic / (traffic_ms * 1e-3) / 1e9) if traffic and traffic_ms else None,
+                             "kernel": "k_wave_trace" if args.pipeline == "v1" else (traffic_kernel or "k_wave2_trace"), "alg_bytes_per_ray": b_alg, "trace_launches": int(st.launches) // 2, "peak_source": peak_src,
+                             "note": "achieved = rays x B_alg / device time of the traversal kernel (CUDA events); these are the input-determined bytes SURVEY 8(d) charges per ray, not bytes moved: camera paths live in registers and the scene is L1/L2 resident, so the fraction can exceed 1 on scenes dominated by camera rays that miss; traffic_gbs is the DRAM rate ncu measured for one launch of the kernel, and the kernel is issue / latency bound (DESIGN.md section 3)"},
                 "clocks": clk}
         if reduce_parity is not None:
             line["reduce_parity"] = reduce_parity
@@ -431,6 +434,10 @@ def run_raybatch(args):
     if rank == 0:
         peak, peak_src = load_peaks()
         b_alg, n_prims = alg_bytes_per_ray(sd)
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("raybatch") or {}
+        except Exception:
+            tr = {}
         rate = n * world * args.steps / (ms * 1e-3)
         st = sc.stats()
         emit({"metric": "Mrays/s", "value": rate / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -441,7 +448,9 @@ def run_raybatch(args):
                           "gpu_launches": int(st.launches), "commit_s": t_commit, "build_ms": st.ms_build, "scene_bytes": int(st.scene_bytes),
                           "parity": {"sah_equals_reference_order": same, "rays_checked": k, "hit_rate": hit_rate},
                           "roofline": {"bound": "hbm", "achieved": rate / world * b_alg / 1e9, "peak": peak, "unit": "GB/s", "frac": rate / world * b_alg / 1e9 / peak,
-                                       "traffic": None, "kernel": "k_trace_batch", "alg_bytes_per_ray": b_alg, "peak_source": peak_src}})
+                                       "traffic": tr.get("bytes"), "traffic_launch_ms": tr.get("launch_ms"), "traffic_source": tr.get("source"),
+                                       "traffic_gbs": (tr["bytes"] / (tr["launch_ms"] * 1e-3) / 1e9) if tr.get("bytes") and tr.get("launch_ms") else None,
+                                       "kernel": "k_trace_batch", "alg_bytes_per_ray": b_alg, "peak_source": peak_src}})
     if dist is not None:
         dist.barrier(); dist.destroy_process_group()
 

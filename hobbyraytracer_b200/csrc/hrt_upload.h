@@ -60,7 +60,9 @@ DScene make_dscene(HostScene& s, Up& up)
     d.wide = (fast && s.tlas_wide.ok) ? 1 : 0;
     for (const DMesh& m : meshes) if (m.ref_root >= 0 && m.wide_root >= 0 && m.wide_nodes == nullptr) d.wide = 0;
     for (size_t i = 0; i < s.mesh_shapes.size(); ++i) if (!s.shapes[(size_t)s.mesh_shapes[i]].wide.ok) d.wide = 0;
-    d.refill_secondary = (fast && !meshes.empty()) ? 1 : 0;
+    // scenes with meshes (long, uneven walks), and scenes whose whole world list fits two levels of the wide top-level tree (a Cornell box
+    // with boxes / media: B200 A/B r2w cornell_smoke 3480 -> 3780 Mrays/s; 485 spheres lose: scattered_balls 5896 -> 3644)
+    d.refill_secondary = (fast && (!meshes.empty() || d.n_objects <= 64)) ? 1 : 0;
     d.big_mesh = 0;
     for (const DMesh& m : meshes) if (m.n_tri >= (int64_t(1) << 17)) d.big_mesh = 1;
     d.tlas_cull_scale = s.tlas_cull_scale;

@@ -459,53 +459,6 @@ __device__ __forceinline__ void acc_flush(FilmAcc& a, long long* film, int pix)
 // Two builds of the same kernel: 128 registers / 4 blocks per SM when camera paths dominate (shiny_teapot: +8 %), 64 registers /
 // 8 blocks per SM when incoherent secondary rays dominate (cornell, scattered balls, teapot_scene: +7-11 %; latency hiding
 // beats spilling there).  The host picks per chunk from the secondary-rays-per-camera-path ratio it reads in the control block.
-// Secondary rays of queue q with per-lane refill (scenes with meshes: the walks are long and their lengths spread widely).
-// Runs before k_wave2_trace, which is then told to skip its own lock-step pass over these entries.
-#ifndef HRT_REFILL_THRESH
-#define HRT_REFILL_THRESH 24
-#endif
-#ifndef HRT_DYN_MIN_BLOCKS
-#define HRT_DYN_MIN_BLOCKS 8
-#endif
-__global__ void __launch_bounds__(BLOCK, HRT_DYN_MIN_BLOCKS) k_wave2_secondary(DScene s, WaveJob j, int q)
-{
-    WaveCtl* c = j.ctl;
-    const unsigned int n_sec = c->n_front[q];
-    if (n_sec == 0) return;
-    const unsigned int lane = threadIdx.x & 31u;
-    const float4* __restrict__ rays = j.rays[q];
-    Walk w; w.live = false; w.pre = 1;
-    bool have = false, exhausted = false;
-    unsigned int e_idx = 0, st = 0; int pix = 0;
-    Collector* none = nullptr;
-    for (;;) {
-        const bool need = !have;
-        const unsigned int m = __ballot_sync(0xffffffffu, need);
-        if (m && !exhausted) {
-            unsigned int base = 0;
-            if (lane == (unsigned int)(__ffs(m) - 1)) base = atomicAdd(&c->sec_next[q], (unsigned int)__popc(m));
-            base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-            const unsigned int my = base + (unsigned int)__popc(m & ((1u << lane) - 1u));
-            if (need && my < n_sec) {
-                float4 a = rays[2 * (size_t)my], b = rays[2 * (size_t)my + 1];
-                Ray r; r.o = v3(a.x, a.y, a.z); r.d = v3(b.x, b.y, b.z);
-                pix = __float_as_int(a.w); st = __float_as_uint(b.w);
-                e_idx = my; have = true;
-                trace_begin(w, s, r, j.t_min, hrt_inf());
-            }
-            if (base + (unsigned int)__popc(m) >= n_sec) exhausted = true;
-        }
-        if (!__any_sync(0xffffffffu, have)) break;
-        const RngKey key = make_key(j.seed, (uint32_t)pix, (uint32_t)(j.s_first + (int)((st >> 8) & 0x7fffffu)), j.rng_mode);
-        walk_run<false, false, true>(w, s, *none, key, st & 0xffu, nullptr, exhausted ? 1 : HRT_REFILL_THRESH);
-        if (have && !w.live) {
-            const Hit h = trace_finish<false>(w, s, key, st & 0xffu, nullptr);
-            if (h.flags & (HIT_RESOLVED | HIT_FALLBACK)) atomicAdd((h.flags & HIT_FALLBACK) ? &c->fallbacks : &c->resolved, 1ull);
-            j.hits[e_idx] = h; have = false;
-        }
-    }
-}
-
 // Camera rays start outside most scenes and the larger part of a frame never comes near an object: such a ray is settled by
 // one slab test against the union of the world-list entries' padded bounds (the boxes the top-level tree is built from),
 // before trace_fast spends three IEEE reciprocals and the entry set-up of a walk on it.  Approximate reciprocals, so the
@@ -545,7 +498,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j
     const unsigned int margin = warps_total * (unsigned int)CLAIM;                // what the other warps may still append after a check
     const unsigned int n_units = wave2_units(j);
     float4* __restrict__ rays = j.rays[q];
-    unsigned int sec_i = skip_secondary ? n_sec + lane : (blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5)) * 32u + lane;   // skip: k_wave2_secondary did them
+    unsigned int sec_i = skip_secondary ? n_sec + lane : (blockIdx.x * (BLOCK / 32) + (threadIdx.x >> 5)) * 32u + lane;   // skip: k_wide_secondary did them
     int c_left = 0, c_sl = 0, c_pix = -1, c_x = 0, c_y = 0;                         // the warp's claim: pixel of this lane, next sample, samples left
     FilmAcc acc; acc.q[0] = acc.q[1] = acc.q[2] = 0; acc.flags = 0;
     for (;;) {
@@ -882,10 +835,10 @@ int wave2_trace_blocks(unsigned int capacity, int sm_count, int minb)
 unsigned long long wave2_total_claims(const WaveJob& j) { return (unsigned long long)wave2_units(j) * (unsigned long long)wave2_sblocks(j); }
 void launch_wave2_trace(const DScene& s, const WaveJob& j, const DCamera& cam, int it, bool secondary_heavy, int sm_count, cudaStream_t st, uint64_t* launches)
 {
-    // per-lane refill pass first when the scene has meshes AND secondary rays dominate (A/B on B200, Mrays/s with / without:
-    // teapot_scene 1199 / 997, but shiny_teapot 7194 / 7715 and the 2.9 M-triangle big mesh 2000 / 2144, whose secondary rays mostly leave at once)
-    const int refill = s.refill_secondary && secondary_heavy;
-    if (refill) { k_wave2_secondary<<<sm_count * HRT_DYN_MIN_BLOCKS, BLOCK, 0, st>>>(s, j, it & 1); *launches += 1; }
+    // scenes without the 8-wide trees (reference-order scenes, unbounded world-list entries, HRT_NO_WIDE): everything in the lock-step kernel.
+    // (Round 1's per-lane-refill pass over the two-child trees - a second hand-kept statement of world_walk - is gone: the wide walk of
+    // launch_wave3_trace took its place, profiles/README.md r2b.)
+    const int refill = 0;
     const bool lens = cam.lens_radius > 0.0f;             // HRT_RENDER_DEFOCUS: the instantiation with the lens sampling compiled in
     if (secondary_heavy) {
         if (lens) k_wave2_trace<8, true, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, it & 1, refill);

@@ -342,154 +342,4 @@ HRT_HD Hit trace_fast(const DScene& s, const Ray& r, float t_min, float t_max, c
     return trace_resolve<COUNT>(s, r, t_min, t_max, key, bounce, cnt, b.bad, b.shear, cull_bound(b));
 }
 
-// ---- resumable walk (per-lane refill kernels only) ------------------------------------------------------------------------------
-// A second statement of world_walk's loop whose state lives in a struct, so that it can return while some lanes of the warp
-// are still walking.  It is NOT used for lock-step callers: keeping the state in a struct costs the lock-step walk 15-25 %
-// (A/B on B200: shiny_teapot 7777 -> 5892 Mrays/s with every walk routed through it), while incoherent rays on meshes gain
-// (16 M-ray batch vs 2.9 M triangles 771 -> 958, teapot_scene 1004 -> 1170).
-// The walk is RESUMABLE: its state lives in a Walk, walk_run() can return while some lanes of the warp are still walking
-// (DYN = true: as soon as fewer than `thresh` lanes are live) so that the kernel refills the idle lanes with new rays and
-// calls it again — a warp of incoherent rays otherwise runs at mean/max of its walk lengths (5 of 32 lanes on
-// teapot_scene, profiles/ r1d).  DYN walks must be called by all 32 lanes together.
-struct Walk {
-    Ray r; V3 rid; float t_min;
-    V3 co, cid; float cull, cull_top; const float4* nodes;           // current level: ray the nodes are tested against, node array, cull scale
-    int obj; Ray lr; TriRay q; bool q_ready; const float4* leaves; uint32_t prim_base;   // mesh level
-    int node, sp; bool live;
-    int pre;                                                          // trace_begin's verdict: 0 walk, 1 no scene, 2 all-NaN origin, 3 unusable ray (trace_ref), 4 reference-order scene (trace_ref)
-    Best b;
-    int stack[WALK_STACK];
-};
-
-HRT_HD void walk_begin(Walk& w, const DScene& s, const Ray& r, const V3 rid, float t_min, float t_max)
-{
-    w.r = r; w.rid = rid; w.t_min = t_min;
-    // RotateQuat objects report t in units of their normalised direction (rotateQuat.cpp:51):
-    // reported t >= world t * |d| * tlas_cull_scale, so entry distances are scaled down before they cull.
-    w.cull_top = s.tlas_cull_scale > 0.0f ? fminf(1.0f, length(r.d) * s.tlas_cull_scale) * 0.9999f : 1.0f;
-    w.co = r.o; w.cid = rid; w.cull = w.cull_top; w.nodes = s.tlas_nodes;
-    w.obj = -1; w.lr = r; w.q.o = r.o; w.q.sX = w.q.sY = w.q.sZ = 0.0f; w.q.kz = 2; w.q_ready = false;
-    w.leaves = nullptr; w.prim_base = 0;
-    w.node = s.tlas_root; w.sp = 0; w.live = true; w.pre = 0;
-    w.b.t = 0.0f; w.b.a = 0.0f; w.b.prim = HRT_MISS; w.b.obj = -1; w.b.amb = 0; w.b.bad = 0; w.b.shear = 0; w.b.t_max = t_max;
-}
-
-template <bool COLLECT, bool COUNT, bool DYN>
-HRT_HD void walk_run(Walk& w, const DScene& s, Collector& k, const RngKey& key, uint32_t bounce, TraceCounters* cnt, int thresh)
-{
-    const float t_lo = fminf(w.t_min, 0.0f);          // ITriangle::hit ignores t_min but only reports t > 0
-    for (;;) {
-#if defined(__CUDA_ARCH__)
-        if (DYN) { if (__popc(__ballot_sync(0xffffffffu, w.live)) < thresh) return; }
-        else if (!w.live) return;
-#else
-        if (!w.live) return;
-#endif
-        if (!w.live) continue;
-        int node = w.node;
-        while (node >= 0) {                                                    // inner nodes of either level
-            const float4* N = w.nodes + 4 * (size_t)node;
-            float4 n0 = HRT_LD4(N), n1 = HRT_LD4(N + 1), n2 = HRT_LD4(N + 2), n3 = HRT_LD4(N + 3);
-            float tn0, tf0, tn1, tf1;
-            slab2(n0, n1, n2, w.co, w.cid, tn0, tf0, tn1, tf1);
-            if (COUNT) cnt->nodes += 2;
-            const float bound = COLLECT ? k.beta : cull_bound(w.b);
-            bool h0 = tn0 <= tf0 && tf0 >= t_lo && (tn0 <= 0.0f || tn0 * w.cull <= bound);
-            bool h1 = tn1 <= tf1 && tf1 >= t_lo && (tn1 <= 0.0f || tn1 * w.cull <= bound);
-            int c0 = float_as_int(n3.x), c1 = float_as_int(n3.y);
-            if (h0 && h1) {
-                if (tn1 < tn0) { int tmp = c0; c0 = c1; c1 = tmp; }
-                if (w.sp < WALK_STACK - 2) w.stack[w.sp++] = c1; else w.b.bad = 1;
-                node = c0;
-            } else if (h0) node = c0;
-            else if (h1) node = c1;
-            else if (w.sp == 0) { w.live = false; break; }
-            else node = w.stack[--w.sp];
-        }
-        if (!w.live) continue;
-        if (node == WALK_MARK) {                                               // the mesh is done: back to the world ray
-            w.co = w.r.o; w.cid = w.rid; w.cull = w.cull_top; w.nodes = s.tlas_nodes; w.obj = -1;
-        } else if (w.obj >= 0) {                                               // a leaf of the mesh tree
-            const uint32_t leaf = (uint32_t)(~node);
-            const float4* L = w.leaves + 8 * (size_t)leaf;
-            const float4 a = HRT_LD4(L), c = HRT_LD4(L + 1);
-            const int triL = float_as_int(a.w), triR = float_as_int(c.w);
-            if (!w.q_ready) { w.q = tri_ray<3>(w.lr, tri_kz(w.lr.o)); w.q_ready = true; }
-            const float bound = COLLECT ? k.beta : cull_bound(w.b);
-            float tL = 0, tR = 0;
-            if (COUNT) cnt->prims += (triR != triL) ? 2 : 1;
-            bool hL = itriangle_t<3>(HRT_LD4(L + 2), HRT_LD4(L + 3), HRT_LD4(L + 4), w.q, bound, tL);
-            bool hR = triR != triL && itriangle_t<3>(HRT_LD4(L + 5), HRT_LD4(L + 6), HRT_LD4(L + 7), w.q, bound, tR);
-            if (hL || hR) {
-                float entry;
-                if (COUNT) cnt->nodes += 1;
-                if (hit_aabb_entry(xyz(a), xyz(c), w.lr, w.t_min, bound, entry)) {   // the reference's bottom node box, its arithmetic
-                    if (COLLECT) {
-                        if (hL) collect(k, tL, w.obj, w.prim_base + (uint32_t)triL, leaf * 2u);
-                        if (hR) collect(k, tR, w.obj, w.prim_base + (uint32_t)triR, leaf * 2u + 1u);
-                    } else {
-                        if (hL) consider(w.b, tL, fmaxf(entry, tL), w.prim_base + (uint32_t)triL, w.obj);
-                        if (hR) consider(w.b, tR, fmaxf(entry, tR), w.prim_base + (uint32_t)triR, w.obj);   // beyond the new bound: no effect
-                    }
-                }
-            }
-        } else {                                                               // a world-list entry
-            const int i = ~node;
-            const DObject& ob = s.objects[i];
-            if (ob.kind == SHAPE_MESH && !ob.medium) {
-                const DMesh& m = s.meshes[ob.mesh];
-                if (m.ref_root >= 0) {
-                    // the three IEEE reciprocals of a ray are computed once per coordinate frame: an unwrapped mesh shares the world ray's
-                    w.lr = w.r; V3 id = w.rid; bool ok = true;
-                    if (ob.xf_count > 0) {
-                        { const Ray wr = w.r; w.lr = to_local(s, ob, wr); }
-                        id = v3(1.0f / w.lr.d.x, 1.0f / w.lr.d.y, 1.0f / w.lr.d.z);
-                        ok = recip_ok(id) && hrt_finite(w.lr.o.x) && hrt_finite(w.lr.o.y) && hrt_finite(w.lr.o.z);
-                    }
-                    if (!ok) w.b.bad = 1;
-                    else if (!COLLECT && !shear_ok(w.lr, tri_kz(w.lr.o))) w.b.shear = 1;    // pass 2 will collect every hit along this ray
-                    else {
-                        if (w.sp < WALK_STACK - 2) w.stack[w.sp++] = WALK_MARK; else w.b.bad = 1;
-                        w.co = w.lr.o; w.cid = id; w.cull = 1.0f; w.nodes = m.fast_nodes; w.leaves = m.fast_leaves; w.prim_base = m.prim_base;
-                        w.obj = i; w.q_ready = false;
-                        if (!w.b.bad) { w.node = m.fast_root; continue; }           // >= 0 node, < 0 leaf: the next turn of the loop
-                    }
-                }
-            } else {
-                float t; uint32_t prim;
-                if (COUNT) cnt->prims += 1;
-                const Ray wr = w.r;                                              // a copy: see trace_finish
-                if (hit_object_ref(s, i, wr, w.t_min, COLLECT ? k.beta : cull_bound(w.b), t, prim, key, bounce)) {
-                    if (COLLECT) collect(k, t, i, prim, 0u); else consider(w.b, t, t, prim, i);
-                }
-            }
-        }
-        if (w.sp == 0 || w.b.bad) { w.live = false; continue; }
-        w.node = w.stack[--w.sp];
-    }
-}
-
-// ---- the same, split for resumable walks: trace_begin -> walk_run<false, ., true> (as often as needed) -> trace_finish -----------
-HRT_HD void trace_begin(Walk& w, const DScene& s, const Ray& r, float t_min, float t_max)
-{
-    const V3 id = v3(1.0f / r.d.x, 1.0f / r.d.y, 1.0f / r.d.z);
-    walk_begin(w, s, r, id, t_min, t_max);
-    if (s.n_objects <= 0) { w.live = false; w.pre = 1; return; }
-    if (!s.fast) { w.live = false; w.pre = 4; return; }                               // HRT_BVH_REFERENCE: no SAH trees, trace_ref answers in trace_finish
-    if (r.o.x != r.o.x && r.o.y != r.o.y && r.o.z != r.o.z) { w.live = false; w.pre = 2; return; }   // see trace_fast
-    if (!(recip_ok(id) && hrt_finite(r.o.x) && hrt_finite(r.o.y) && hrt_finite(r.o.z))) { w.live = false; w.pre = 3; w.b.bad = 1; }
-}
-template <bool COUNT>
-HRT_HD Hit trace_finish(const Walk& w, const DScene& s, const RngKey& key, uint32_t bounce, TraceCounters* cnt)
-{
-    Hit h; h.t = 0.0f; h.prim = HRT_MISS; h.obj = -1; h.flags = 0;
-    if (w.pre == 1) return h;
-    const Ray r = w.r;                  // a copy: handing &w.r to an out-of-line function would pin the whole Walk in local memory
-    if (w.pre == 4) return trace_ref(s, r, w.t_min, w.b.t_max, key, bounce);
-    if (w.pre == 2) { if (s.nan_obj >= 0) { h.t = int_as_float(0x7fc00000); h.prim = s.nan_prim; h.obj = s.nan_obj; } return h; }
-    const Best& b = w.b;
-    if (!b.bad && !b.amb && !b.shear) { h.t = b.prim == HRT_MISS ? 0.0f : b.t; h.prim = b.prim; h.obj = b.obj; return h; }
-    return trace_resolve<COUNT>(s, r, w.t_min, b.t_max, key, bounce, cnt, b.bad, b.shear, cull_bound(b));
-}
-
 } // namespace hrt

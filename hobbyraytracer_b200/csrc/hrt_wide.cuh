@@ -78,15 +78,16 @@ HRT_HD float4 wide_f4(uint32_t x, uint32_t y, uint32_t z) { float4 r; r.x = wide
 struct WRay {
     V3 o, id;
     uint32_t neg;       // bit a: d[a] < 0 (the child's hi plane is the near one)
-    uint32_t oct;       // bit a: d[a] > 0; slot ^ oct = 7 for the nearest octant, 0 for the farthest
 };
+// A ray is only walked when the reciprocals of its direction are finite (wide_begin, wide_mesh_step): no component is zero or NaN, so
+// "d[a] < 0" is the sign bit and "d[a] > 0" its complement.
 HRT_HD WRay wide_ray(V3 o, V3 d, V3 id)
 {
     WRay q; q.o = o; q.id = id;
-    q.neg = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
-    q.oct = (d.x > 0.0f ? 1u : 0u) | (d.y > 0.0f ? 2u : 0u) | (d.z > 0.0f ? 4u : 0u);
+    q.neg = ((uint32_t)float_as_int(d.x) >> 31) | (((uint32_t)float_as_int(d.y) >> 31) << 1) | (((uint32_t)float_as_int(d.z) >> 31) << 2);
     return q;
 }
+HRT_HD uint32_t wide_oct(const WRay& q) { return q.neg ^ 7u; }    // bit a: d[a] > 0; slot ^ oct = 7 for the nearest octant, 0 for the farthest
 
 // Slab test of the eight children of a node: bit s of the result is set when the ray MAY pass through slot s's box within
 // [t_lo, bnd0].  c0 / c1 are the first 64 bytes of the node.
@@ -184,20 +185,23 @@ HRT_HD int wide_fls(uint32_t m)
 // The group travels in L.cur (dead between a step and the pop): steps leave it there, 0 for "none".
 template <class St> HRT_HD void wide_pop(WideLane& L, const DScene& s, St& st)
 {
-    for (;;) {
-        uint32_t v = (uint32_t)L.cur; L.cur = 0;
-        if (v == 0u) {
-            if (st.empty() || L.b.bad) { L.live = false; return; }
+    // (no loop: a marker is never followed by another one - meshes are only entered from the top level - and a loop around
+    // wide_enter_top made the compiler shuffle the whole lane state through a second register set, 18 % of teapot_scene's instructions, r2z)
+    uint32_t v = (uint32_t)L.cur; L.cur = 0;
+    if (v == 0u) {
+        if (st.empty() || L.b.bad) { L.live = false; return; }
+        v = (uint32_t)st.top(); st.drop();
+        if (v == (uint32_t)WALK_MARK) {                                                   // the mesh is done: back to the world ray
+            wide_enter_top(L, s);
+            if (st.empty()) { L.live = false; return; }
             v = (uint32_t)st.top(); st.drop();
-            if (v == (uint32_t)WALK_MARK) { wide_enter_top(L, s); continue; }            // the mesh is done: back to the world ray
         }
-        uint32_t mp = v & 0xffu; const uint32_t node = v >> 8;
-        const int k = wide_fls(mp);
-        mp &= ~(1u << k);
-        if (mp && !st.push((int)((node << 8) | mp))) { L.b.bad = 1; L.live = false; return; }
-        L.cur = wide_ld_child(L.nodes, node, (uint32_t)k ^ L.q.oct);
-        return;
     }
+    uint32_t mp = v & 0xffu; const uint32_t node = v >> 8;
+    const int k = wide_fls(mp);
+    mp &= ~(1u << k);
+    if (mp && !st.push((int)((node << 8) | mp))) { L.b.bad = 1; L.live = false; return; }
+    L.cur = wide_ld_child(L.nodes, node, (uint32_t)k ^ wide_oct(L.q));
 }
 
 // Starts the walk of ray r.  Returns false when pass 1 has nothing to walk (L.live stays false): no scene, an all-NaN origin
@@ -232,7 +236,7 @@ HRT_HD void wide_node_step(WideLane& L)
     const W32 c0 = wide_ld32(N), c1 = wide_ld32(N + 32);
     wide_prefetch(N + 64);
     const float t_lo = fminf(L.t_min, 0.0f);                                    // ITriangle::hit ignores t_min but only reports t > 0
-    const uint32_t mp = wide_xor_bits(wide_hits(c0, c1, L.q, t_lo, L.bnd0), L.q.oct);
+    const uint32_t mp = wide_xor_bits(wide_hits(c0, c1, L.q, t_lo, L.bnd0), wide_oct(L.q));
     L.cur = mp ? (int)((node << 8) | mp) : 0;
 }
 

@@ -39,8 +39,28 @@ __device__ __forceinline__ RngKey make_key(uint64_t seed, uint32_t index, uint32
 #define HRT_BATCH_MIN_BLOCKS 5      // 96 registers: ray batch 1355 (4 blocks) / 1493 (5) / 1453 (6) / 1078 (8) Mrays/s on B200 (profiles/README.md r2f)
 #endif
 // Pending rays (pass 1 could not decide: hrt_wide.cuh) are listed here and settled by k_resolve_* afterwards.
-struct PendList { unsigned int* idx; unsigned int* count; };
-__device__ __forceinline__ void pend_push(const PendList& p, unsigned int i) { p.idx[atomicAdd(p.count, 1u)] = i; }
+struct PendList { unsigned int* idx; unsigned int* count; unsigned int cap; };
+
+// ---- bounds-checked build (-DHRT_BOUNDS_CHECK, tools/build_variant.sh bounds "-DHRT_BOUNDS_CHECK") ------------------------------------
+// compute-sanitizer is closed on the GPU pool this was developed on, so the indexed stores of the queue machinery carry their own
+// checks in a variant build: an index outside its array is counted per site and the store is skipped; tools/sanitize_case.py runs
+// every kernel family on small cases against that build and expects all counters at zero (site 7 is the self test: it must count).
+// In the product build HRT_IN_BOUNDS is the constant true.
+#if defined(HRT_BOUNDS_CHECK)
+__device__ unsigned int g_bounds[8];
+__device__ __forceinline__ bool bounds_ok(unsigned long long i, unsigned long long n, int site) { if (i < n) return true; atomicAdd(&g_bounds[site], 1u); return false; }
+#define HRT_IN_BOUNDS(i, n, site) bounds_ok((unsigned long long)(i), (unsigned long long)(n), site)
+__global__ void k_bounds_selftest() { if (HRT_IN_BOUNDS(5, 3, 7)) g_bounds[6] = 0xdeadu; }
+#else
+#define HRT_IN_BOUNDS(i, n, site) true
+#endif
+enum { BS_PEND = 0, BS_CAMERA_APPEND = 1, BS_SHADE_APPEND = 2, BS_FILM = 3, BS_HITS = 4, BS_BATCH_HITS = 5 };
+
+__device__ __forceinline__ void pend_push(const PendList& p, unsigned int i)
+{
+    const unsigned int k = atomicAdd(p.count, 1u);
+    if (HRT_IN_BOUNDS(k, p.cap, BS_PEND)) p.idx[k] = i;
+}
 
 // Persistent warps over the 8-wide trees: a lane whose walk is over takes the next ray from a global counter while the other
 // lanes keep theirs, and the warp advances in phases (hrt_wide.cuh).  Scenes without wide trees: one ray per thread (_plain).
@@ -67,7 +87,7 @@ __global__ void __launch_bounds__(BLOCK, HRT_BATCH_MIN_BLOCKS) k_trace_batch(DSc
         if (walking < (exhausted ? 1 : HRT_WIDE_REFILL)) {
             if (idx >= 0 && !L.live) {                                            // a finished walk: its record, or its place on the pending list
                 const Hit h = wide_result(L);
-                hits[idx] = h;
+                if (HRT_IN_BOUNDS(idx, n, BS_BATCH_HITS)) hits[idx] = h;
                 if (h.flags & HIT_PENDING) pend_push(pend, (unsigned int)idx);
                 idx = -1;
             }
@@ -173,8 +193,9 @@ __device__ __forceinline__ void count_clamped(unsigned long long* counter, float
 {
     if (fabsf(v) > (float)(1 << FILM_MAG_BITS) && fabsf(v) <= 3.402823466e+38f) atomicAdd(counter, 1ull);
 }
-__device__ __forceinline__ void film_add(long long* film, int pix, V3 c, unsigned long long* clamped)
+__device__ __forceinline__ void film_add(long long* film, int pix, V3 c, unsigned long long* clamped, int npix)
 {
+    if (!HRT_IN_BOUNDS(pix, npix, BS_FILM)) return;
     long long* px = film + (size_t)pix * FILM_LANES;
     const float v[3] = {c.x, c.y, c.z};
 #pragma unroll
@@ -376,7 +397,7 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave_shade(DScene s, WaveJob j,
             go = go && (int)bounce + 1 < j.max_depth;                           // MAX_DEPTH reached: the partial sum stands (main.cpp:43,78)
             if (go) st = pack_state(sl, (int)bounce + 1, has_result);
             else {
-                if (has_result) film_add(j.film, pix, result, &c->clamped);                  // px += rayColour(...)  main.cpp:123
+                if (has_result) film_add(j.film, pix, result, &c->clamped, j.npix);                  // px += rayColour(...)  main.cpp:123
                 fresh = true;
             }
         }
@@ -448,8 +469,9 @@ __device__ __forceinline__ void acc_add(FilmAcc& a, V3 c, unsigned long long* cl
         a.q[ch] += q; a.flags |= flag;
     }
 }
-__device__ __forceinline__ void acc_flush(FilmAcc& a, long long* film, int pix)
+__device__ __forceinline__ void acc_flush(FilmAcc& a, long long* film, int pix, int npix)
 {
+    if (!HRT_IN_BOUNDS(pix, npix, BS_FILM)) return;
     long long* px = film + (size_t)pix * FILM_LANES;
 #pragma unroll
     for (int ch = 0; ch < 3; ++ch) if (a.q[ch] != 0) { atomicAdd((unsigned long long*)(px + ch), (unsigned long long)a.q[ch]); a.q[ch] = 0; }
@@ -514,7 +536,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j
         } else {
             primary = true;
             if (c_left == 0) {
-                if (c_pix >= 0) acc_flush(acc, j.film, c_pix);
+                if (c_pix >= 0) acc_flush(acc, j.film, c_pix, j.npix);
                 unsigned long long k0 = 0;
                 if (lane == 0 && ld_relaxed(&c->n_prim[q]) + margin <= room && ld_relaxed(&c->next_path) < total_claims)
                     k0 = atomicAdd(&c->next_path, 1ull) + 1ull;
@@ -559,7 +581,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j
         } else if (walk) h = s.fast ? trace_fast<false>(s, r, j.t_min, hrt_inf(), key, st & 0xffu, nullptr) : trace_ref(s, r, j.t_min, hrt_inf(), key, st & 0xffu);
         if (h.flags & (HIT_RESOLVED | HIT_FALLBACK)) atomicAdd((h.flags & HIT_FALLBACK) ? &c->fallbacks : &c->resolved, 1ull);
         if (!primary) {
-            if (active) j.hits[sec_i] = h;
+            if (active && HRT_IN_BOUNDS(sec_i, j.capacity, BS_HITS)) j.hits[sec_i] = h;
             sec_i += stride;
             continue;
         }
@@ -572,9 +594,11 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j
             e0 = __shfl_sync(0xffffffffu, e0, 0);
             if (hit) {
                 const unsigned int e = n_sec + e0 + (unsigned int)__popc(m_hit & ((1u << lane) - 1u));
-                rays[2 * (size_t)e] = make_float4(r.o.x, r.o.y, r.o.z, __int_as_float(pix));
-                rays[2 * (size_t)e + 1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(st));
-                j.hits[e] = h;
+                if (HRT_IN_BOUNDS(e, j.capacity, BS_CAMERA_APPEND)) {
+                    rays[2 * (size_t)e] = make_float4(r.o.x, r.o.y, r.o.z, __int_as_float(pix));
+                    rays[2 * (size_t)e + 1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(st));
+                    j.hits[e] = h;
+                }
             }
         }
     }
@@ -612,7 +636,7 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave2_shade(DScene s, WaveJob j
             go = go && (int)bounce + 1 < j.max_depth;                               // MAX_DEPTH reached: the partial sum stands (main.cpp:43,78)
             if (RR) go = go && russian_roulette(atten, key, bounce);                // opt-in, separate instantiation: the default kernel is unchanged
             if (go) st = pack_state(sl, (int)bounce + 1, has_result);
-            else if (has_result) film_add(j.film, pix, result, &c->clamped);                     // px += rayColour(...)  main.cpp:123
+            else if (has_result) film_add(j.film, pix, result, &c->clamped, j.npix);                     // px += rayColour(...)  main.cpp:123
         }
         const unsigned int m_go = __ballot_sync(0xffffffffu, go);
         if (lane == 0) w_go[warp] = (unsigned int)__popc(m_go);
@@ -626,10 +650,12 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave2_shade(DScene s, WaveJob j
         __syncthreads();
         if (go) {
             const unsigned int e2 = s_pos + w_go[warp] + (unsigned int)__popc(m_go & ((1u << lane) - 1u));
-            j.rays[o][2 * (size_t)e2] = make_float4(r.o.x, r.o.y, r.o.z, __int_as_float(pix));
-            j.rays[o][2 * (size_t)e2 + 1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(st));
-            j.thr[o][e2] = make_float4(atten.x, atten.y, atten.z, 0.0f);
-            if (has_result) j.res[o][e2] = make_float4(result.x, result.y, result.z, 0.0f);
+            if (HRT_IN_BOUNDS(e2, j.capacity, BS_SHADE_APPEND)) {
+                j.rays[o][2 * (size_t)e2] = make_float4(r.o.x, r.o.y, r.o.z, __int_as_float(pix));
+                j.rays[o][2 * (size_t)e2 + 1] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(st));
+                j.thr[o][e2] = make_float4(atten.x, atten.y, atten.z, 0.0f);
+                if (has_result) j.res[o][e2] = make_float4(result.x, result.y, result.z, 0.0f);
+            }
         }
         __syncthreads();                                                            // the next pass of the loop rewrites the shared counters
     }
@@ -650,7 +676,7 @@ __global__ void __launch_bounds__(BLOCK, HRT_WSEC_MIN_BLOCKS) k_wide_secondary(D
     WideSmemStack<BLOCK> st; st.base = stack_mem + threadIdx.x; st.sp = 0;
     const unsigned int lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
     const float4* __restrict__ rays = j.rays[q];
-    PendList pend; pend.idx = j.pend; pend.count = &c->pend_count;
+    PendList pend; pend.idx = j.pend; pend.count = &c->pend_count; pend.cap = j.capacity;
     WideLane L; L.live = false;
     bool have = false, exhausted = false;
     unsigned int e_idx = 0, r_st = 0; int r_pix = 0;
@@ -659,7 +685,7 @@ __global__ void __launch_bounds__(BLOCK, HRT_WSEC_MIN_BLOCKS) k_wide_secondary(D
         if (walking < (exhausted ? 1 : HRT_WIDE_REFILL)) {
             if (have && !L.live) {
                 const Hit h = wide_result(L);
-                j.hits[e_idx] = h;
+                if (HRT_IN_BOUNDS(e_idx, j.capacity, BS_HITS)) j.hits[e_idx] = h;
                 if (h.flags & HIT_PENDING) pend_push(pend, e_idx);
                 have = false;
             }
@@ -724,7 +750,7 @@ __global__ void __launch_bounds__(BLOCK) k_render_mega(DScene s, WaveJob j, DCam
             if (go && j.rr && b + 1 < j.max_depth) go = russian_roulette(atten, key, (uint32_t)b);
             if (!go) break;
         }
-        if (has_result) film_add(j.film, pix, result, &j.ctl->clamped);
+        if (has_result) film_add(j.film, pix, result, &j.ctl->clamped, j.npix);
     }
     if (rays) atomicAdd(&j.ctl->rays, rays);
 }
@@ -745,7 +771,7 @@ void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit*
 {
     cudaMemsetAsync(d_counter, 0, sizeof(unsigned long long), st);
     cudaMemsetAsync(d_pend_count, 0, sizeof(unsigned int), st);
-    PendList pend; pend.idx = d_pend_idx; pend.count = d_pend_count;
+    PendList pend; pend.idx = d_pend_idx; pend.count = d_pend_count; pend.cap = (unsigned int)(n < 0xffffffffll ? n : 0xffffffffll);
     if (!s.wide || getenv("HRT_NO_WIDE")) { k_trace_batch_plain<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed); *launches += 1; return; }
     k_trace_batch<<<grid_for(n, sm_count, HRT_BATCH_MIN_BLOCKS), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed, d_counter, pend);
     k_resolve_batch<<<sm_count * 8, BLOCK, 0, st>>>(s, d_rays, d_hits, seed, pend); *launches += 2;
@@ -909,3 +935,16 @@ void launch_film_resolve(const long long* d_film, int npix, int spp, float* d_su
 }
 
 } // namespace hrt
+
+#if defined(HRT_BOUNDS_CHECK)
+// bounds-checked variant only: runs the self test, copies the per-site violation counters out and clears them
+extern "C" int hrt_debug_bounds(unsigned int* out8)
+{
+    hrt::k_bounds_selftest<<<1, 1>>>();
+    if (cudaDeviceSynchronize() != cudaSuccess) return -3;
+    if (cudaMemcpyFromSymbol(out8, hrt::g_bounds, 8 * sizeof(unsigned int)) != cudaSuccess) return -3;
+    unsigned int zero[8] = {0};
+    if (cudaMemcpyToSymbol(hrt::g_bounds, zero, sizeof(zero)) != cudaSuccess) return -3;
+    return 0;
+}
+#endif

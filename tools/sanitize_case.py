@@ -35,5 +35,32 @@ x = np.random.default_rng(0).normal(size=(1000, 14)).astype(np.float32)
 g.scatter(0, x, np.ones(1000, np.uint8), seed=1)
 g.texture_eval(0, np.random.default_rng(1).random((1000, 5)).astype(np.float32))
 g.close()
+# queues under pressure: 2 M camera paths through queues of 2^18 entries (the append margins and the "conservatively full" logic work hardest here),
+# wavefront == megakernel bit for bit
+os.environ["HRT_WAVE_CAPACITY"] = str(1 << 18)
+for make in (lambda: scenes.teapot_scene(cache, n=16, env_w=64, env_h=32)[:2], lambda: scenes.cornell_smoke_scene(glass_sphere=True)[:2]):
+    sdp, camp = make()
+    gp = sdp.build(lib, abi.BVH_SAH, 3)
+    cp = scenes.camera_for(camp, 512, 512)
+    a = gp.render(cp, 512, 512, 8, seed=11)[0]
+    b = gp.render(cp, 512, 512, 8, seed=11, flags=abi.RENDER_MEGAKERNEL)[0]
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), "queues under pressure: wavefront != megakernel"
+    gp.close()
+del os.environ["HRT_WAVE_CAPACITY"]
 lib.fn("trim")()
+# bounds-checked variant (HRT_PRODUCT_SO=hobbyraytracer_b200/csrc/variants/libhrt_b200_bounds.so, built by tools/build_variant.sh bounds
+# "-DHRT_BOUNDS_CHECK"): every indexed store of the queue machinery counted an index outside its array instead of writing; site 7 is the
+# self test and must have fired once, every other counter must be zero
+import ctypes as C
+try:
+    f = lib.dll.hrt_debug_bounds
+except AttributeError:
+    f = None
+if f is not None:
+    out = (C.c_uint * 8)()
+    assert f(out) == 0
+    counts = list(out)
+    print("bounds counters (pending list, camera append, shade append, film, hit records, batch hit records, -, self test):", counts)
+    assert counts[7] == 1 and counts[6] == 0 and not any(counts[:6]), counts
+    print("bounds check ok: no index left its array")
 print("sanitize_case ok")

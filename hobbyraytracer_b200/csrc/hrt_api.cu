@@ -625,6 +625,22 @@ int hrt_trace_batch(hrt_scene* s, const float* rays, int64_t n, uint32_t* prim_i
     return 0;
 }
 
+// ---- parity entry for Camera::getRay (camera.h:9-39): needs no scene, runs on the device selected by hrt_set_device ----------------------
+int hrt_camera_rays(const hrt_camera* cam, const float* st, int64_t n, float* out)
+{
+    if (!cam || n < 0 || (n > 0 && (!st || !out))) { g_err = "bad argument"; return HRT_ERR_ARG; }
+    if (n == 0) return 0;
+    CK(cudaSetDevice(g_device));
+    int sms = 148; cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, g_device);
+    DevBuf in, res;
+    CK(in.alloc(sizeof(float) * 2 * (size_t)n)); CK(res.alloc(sizeof(float) * 6 * (size_t)n));
+    CK(cudaMemcpy(in.p, st, sizeof(float) * 2 * (size_t)n, cudaMemcpyHostToDevice));
+    launch_camera_rays(make_camera(*cam), (const float*)in.p, n, (float*)res.p, sms, nullptr);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out, res.p, sizeof(float) * 6 * (size_t)n, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
 // ---- parity entries for the shading half of the path: Texture::colourValue and Material::scatter / emitted on batches ----------------
 int hrt_texture_eval(hrt_scene* s, int texture, const float* uvp, int64_t n, float* out_rgb)
 {

@@ -158,6 +158,16 @@ __global__ void __launch_bounds__(BLOCK) k_eval_batch(DScene s, const float4* __
 }
 
 // ---- Texture::colourValue / Material::scatter + emitted on caller-supplied batches (parity entries, like K7 for hit()) -----------------
+// Camera::getRay(s, t) on a batch (camera.h:32-39; parity entry hrt_camera_rays): out = origin xyz, direction xyz (not normalised)
+__global__ void __launch_bounds__(BLOCK) k_camera_rays(DCamera cam, const float* __restrict__ st, long long n, float* __restrict__ out)
+{
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const Ray r = camera_ray<false>(cam, st[2 * i], st[2 * i + 1]);
+        float* o = out + 6 * i;
+        o[0] = r.o.x; o[1] = r.o.y; o[2] = r.o.z; o[3] = r.d.x; o[4] = r.d.y; o[5] = r.d.z;
+    }
+}
 __global__ void __launch_bounds__(BLOCK) k_texture_eval(DScene s, int tex, const float* __restrict__ in, long long n, float* __restrict__ out)
 {
     const long long stride = (long long)gridDim.x * blockDim.x;
@@ -812,6 +822,10 @@ cudaError_t launch_trace_batch_static(const DScene& s, int device, const float4*
     launch_trace_batch(s, d_rays, n, hits, seed, counter, pend_idx, pend_count, sm_count, st, launches);
     launch_split_hits(hits, n, d_prim, d_t, sm_count, st, launches);
     return cudaGetLastError();
+}
+void launch_camera_rays(const DCamera& cam, const float* d_st, long long n, float* d_out, int sm_count, cudaStream_t st)
+{
+    k_camera_rays<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(cam, d_st, n, d_out);
 }
 void launch_texture_eval(const DScene& s, int tex, const float* d_in, long long n, float* d_out, int sm_count, cudaStream_t st, uint64_t* launches)
 {

@@ -62,6 +62,7 @@ void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit*
 #define HRT_STATIC_MAX_DEVICES 64
 cudaError_t launch_trace_batch_static(const DScene& s, int device, const float4* d_rays, long long n, uint32_t* d_prim, float* d_t, uint64_t seed,
                                       int sm_count, cudaStream_t st, uint64_t* launches);
+void launch_camera_rays(const DCamera& cam, const float* d_st, long long n, float* d_out, int sm_count, cudaStream_t st);
 void launch_texture_eval(const DScene& s, int tex, const float* d_in, long long n, float* d_out, int sm_count, cudaStream_t st, uint64_t* launches);
 void launch_scatter_batch(const DScene& s, int material, const float* d_in, const uint8_t* d_front, long long n, uint64_t seed, int rng_mode, float* d_out,
                           int sm_count, cudaStream_t st, uint64_t* launches);

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define HRT_ABI_VERSION 6
+#define HRT_ABI_VERSION 7
 
 /* ---- error codes --------------------------------------------------------------------------- */
 #define HRT_OK            0
@@ -242,6 +242,9 @@ int hrt_trace_batch_static(hrt_scene* s, const void* d_rays, int64_t n, void* d_
  *   records; in14: n x 14 floats (r_in.origin, r_in.dir, rec.p, rec.normal, rec.u, rec.v), front: n bytes (rec.frontFace); out10:
  *   n x 10 floats (scattered ? 1 : 0, attenuation rgb, scattered.dir, emitted rgb).  Record i draws from the Philox stream of
  *   (seed; index i, sample 0) at bounce 0, rng_mode as in hrt_render_params. */
+/* hrt_camera_rays: Camera::getRay(s, t) of Camera(cam) (camera.h:9-39; the lens offset is zero like the reference's) on n (s, t) pairs, computed on
+ * the device: out = n x 6 floats (origin xyz, direction xyz - not normalised).  Needs no scene; runs on the device of hrt_set_device. */
+int hrt_camera_rays(const hrt_camera* cam, const float* st, int64_t n, float* out);
 int hrt_texture_eval(hrt_scene* s, int texture, const float* uvp, int64_t n, float* out_rgb);
 int hrt_scatter_batch(hrt_scene* s, int material, const float* in14, const uint8_t* front, int64_t n, uint64_t seed, int rng_mode, float* out10);
 

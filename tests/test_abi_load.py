@@ -22,7 +22,7 @@ def test_exports_every_declared_symbol(hrt):
     assert len(syms) >= 28
     missing = [s for s in syms if not hasattr(hrt.dll, s)]
     assert not missing, f"libhrt_b200.so does not export {missing}"
-    assert hrt.fn("abi_version")() == 6
+    assert hrt.fn("abi_version")() == 7
 
 
 def test_builder_errors_and_state(hrt):

@@ -106,6 +106,16 @@ def test_gpu_matches_reference_fixture(hrt, name, mode):
 
 
 @pytest.mark.gpu
+def test_gpu_camera_rays_match_reference_fixture(hrt):
+    """Camera::getRay on the device (hrt_camera_rays) against the rays the unmodified reference produced (host_kats.npz): bit for bit."""
+    k = load("host_kats.npz")
+    cam = scenes.camera_for(cases.RENDER_CAMERA, 48, 32)
+    out = np.empty((len(k["cam_st"]), 6), np.float32)
+    hrt.check(hrt.fn("camera_rays")(abi.C.byref(cam), abi._ptr(k["cam_st"]), len(out), abi._ptr(out)), "camera_rays")
+    assert np.array_equal(bits(out), bits(k["cam_rays"]))
+
+
+@pytest.mark.gpu
 def test_gpu_film_resolve_matches_reference_fixture(hrt):
     """hrt_render's resolve (mean -> ACES -> sqrt -> 8 bit, film.cpp:25-52) against the reference's bytes: a scene that is
     only a constant background makes every pixel sum = spp * colour, so the 8-bit image is a pure function of the film code."""

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(BLOCK, HRT_BATCH_MIN_BLOCKS) k_trace_batch(DSc
     long long idx = -1; bool exhausted = false;
     for (;;) {
         const int walking = __popc(__ballot_sync(0xffffffffu, L.live));
-        if (walking < (exhausted ? 1 : HRT_WIDE_REFILL)) {
+        if (walking < (exhausted ? 1 : s.wide_refill)) {
             if (idx >= 0 && !L.live) {                                            // a finished walk: its record, or its place on the pending list
                 const Hit h = wide_result(L);
                 if (HRT_IN_BOUNDS(idx, n, BS_BATCH_HITS)) hits[idx] = h;
@@ -692,7 +692,7 @@ __global__ void __launch_bounds__(BLOCK, HRT_WSEC_MIN_BLOCKS) k_wide_secondary(D
     unsigned int e_idx = 0, r_st = 0; int r_pix = 0;
     for (;;) {
         const int walking = __popc(__ballot_sync(0xffffffffu, L.live));
-        if (walking < (exhausted ? 1 : HRT_WIDE_REFILL)) {
+        if (walking < (exhausted ? 1 : s.wide_refill)) {
             if (have && !L.live) {
                 const Hit h = wide_result(L);
                 if (HRT_IN_BOUNDS(e_idx, j.capacity, BS_HITS)) j.hits[e_idx] = h;

@@ -385,12 +385,9 @@ HRT_HDN inline Hit wide_trace_scalar(const DScene& s, const Ray& r, float t_min,
 
 // ---- a warp of lanes (device only) ------------------------------------------------------------------------------------------------
 #if defined(__CUDACC__)
-#ifndef HRT_WIDE_PHASE_MIN
-#define HRT_WIDE_PHASE_MIN 8       // a phase runs when at least this many lanes wait for it (or nothing larger can run)
-#endif
-#ifndef HRT_WIDE_REFILL
-#define HRT_WIDE_REFILL 24         // idle lanes take new rays as soon as fewer than this many lanes are walking
-#endif
+// Thresholds of a warp's rounds, per scene (DScene::wide_phase_min / wide_refill, set at commit in hrt_upload.h; B200 A/B r2c, r3d):
+// a phase runs when at least wide_phase_min lanes wait for it (or nothing larger can run); idle lanes take new rays as soon as fewer
+// than wide_refill lanes are walking.
 
 // One column of a shared-memory array per thread: entry k of thread t lives at base[k * THREADS], so the lanes of a warp
 // hit 32 different banks whatever their stack depths.
@@ -419,7 +416,7 @@ __device__ __forceinline__ bool wide_round(WideLane& L, const DScene& s, St& st,
     const int n_me = __popc(__ballot_sync(0xffffffffu, w_me)), n_ob = __popc(__ballot_sync(0xffffffffu, w_ob));
     const int most = max(max(n_in, n_tl), max(n_me, n_ob));
     if (most == 0) return false;
-    const int need = most < HRT_WIDE_PHASE_MIN ? most : HRT_WIDE_PHASE_MIN;
+    const int need = most < s.wide_phase_min ? most : s.wide_phase_min;
     bool pop = false;
     if (n_in >= need) { if (w_in) { wide_node_step(L); pop = true; } }
     if (n_tl >= need) { if (w_tl) { wide_leaf_step(L); pop = true; } }

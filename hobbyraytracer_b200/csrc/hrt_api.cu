@@ -530,6 +530,7 @@ int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed)
     DevUp up(s->scene_allocs, s->scene_alloc_bytes, s->device);
     s->d = make_dscene(s->host, up);
     if (const char* e = getenv("HRT_WIDE_PHASE_MIN")) { int v = atoi(e); if (v >= 1 && v <= 32) s->d.wide_phase_min = v; }          // A/B overrides
+    if (const char* e = getenv("HRT_WIDE_PHASE_MIN_OBJ")) { int v = atoi(e); if (v >= 1 && v <= 32) s->d.wide_phase_min_obj = v; }
     if (const char* e = getenv("HRT_WIDE_REFILL")) { int v = atoi(e); if (v >= 1 && v <= 32) s->d.wide_refill = v; }
     if (const char* e = getenv("HRT_REFILL_SECONDARY")) s->d.refill_secondary = (atoi(e) != 0 && s->d.fast) ? 1 : 0;   // A/B override
     if (up.failed) { g_err = "scene upload failed: " + up.msg; free_scene_device(s); return HRT_ERR_CUDA; }
@@ -973,7 +974,7 @@ int make_replica(hrt_scene* s, int device, hrt_scene** out)
     DevUp up(r->scene_allocs, r->scene_alloc_bytes, device);
     up.dev_override = &r->dev_meshes;
     r->d = make_dscene(s->host, up);
-    r->d.refill_secondary = s->d.refill_secondary; r->d.wide_phase_min = s->d.wide_phase_min; r->d.wide_refill = s->d.wide_refill;
+    r->d.refill_secondary = s->d.refill_secondary; r->d.wide_phase_min = s->d.wide_phase_min; r->d.wide_phase_min_obj = s->d.wide_phase_min_obj; r->d.wide_refill = s->d.wide_refill;
     if (up.failed) return fail("replica upload failed: " + up.msg);
     r->scene_bytes += up.bytes;
     e = cudaDeviceSynchronize();

@@ -416,12 +416,13 @@ __device__ __forceinline__ bool wide_round(WideLane& L, const DScene& s, St& st,
     const int n_me = __popc(__ballot_sync(0xffffffffu, w_me)), n_ob = __popc(__ballot_sync(0xffffffffu, w_ob));
     const int most = max(max(n_in, n_tl), max(n_me, n_ob));
     if (most == 0) return false;
-    const int need = most < s.wide_phase_min ? most : s.wide_phase_min;
+    // a phase runs when enough lanes wait for it, or when no phase has more (the largest group always runs: progress)
+    const int thr = s.wide_phase_min, thr_ob = s.wide_phase_min_obj;
     bool pop = false;
-    if (n_in >= need) { if (w_in) { wide_node_step(L); pop = true; } }
-    if (n_tl >= need) { if (w_tl) { wide_leaf_step(L); pop = true; } }
-    if (n_me >= need) { if (w_me) pop = wide_mesh_step(L, s, st); }
-    if (n_ob >= need) { if (w_ob) { wide_object_step(L, s, key, bounce); pop = true; } }
+    if (n_in >= thr || n_in == most) { if (w_in) { wide_node_step(L); pop = true; } }
+    if (n_tl >= thr || n_tl == most) { if (w_tl) { wide_leaf_step(L); pop = true; } }
+    if (n_me >= thr_ob || n_me == most) { if (w_me) pop = wide_mesh_step(L, s, st); }
+    if (n_ob >= thr_ob || n_ob == most) { if (w_ob) { wide_object_step(L, s, key, bounce); pop = true; } }
     if (pop) wide_pop(L, s, st);
     return true;
 }

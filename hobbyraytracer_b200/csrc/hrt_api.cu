@@ -728,12 +728,13 @@ int hrt_render(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, 
 // ---- checkpoints (hrt_render_progressive) ------------------------------------------------------------------------
 namespace {
 struct CheckpointHeader {
-    char     magic[8];            // "HRTFILM1"
+    char     magic[8];            // "HRTFILM2"
     int32_t  width, height, spp, samples_done, max_depth, rng_mode, flags_reserved;
     float    t_min;
     uint64_t seed, camera_hash, prim_count;
+    uint64_t scene_hash;          // HostScene::content_hash: objects, wrappers, materials, textures, geometry, background, BVH mode
 };
-const char kCheckpointMagic[8] = {'H', 'R', 'T', 'F', 'I', 'L', 'M', '1'};
+const char kCheckpointMagic[8] = {'H', 'R', 'T', 'F', 'I', 'L', 'M', '2'};
 uint64_t fnv1a(const void* p, size_t n) { const unsigned char* b = (const unsigned char*)p; uint64_t h = 1469598103934665603ull; for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; } return h; }
 CheckpointHeader checkpoint_header_of(const hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p)
 {
@@ -742,13 +743,13 @@ CheckpointHeader checkpoint_header_of(const hrt_scene* s, const hrt_camera* cam,
     h.width = p->width; h.height = p->height; h.spp = p->spp; h.samples_done = 0;
     h.max_depth = p->max_depth > 0 ? p->max_depth : 50; h.rng_mode = p->rng_mode; h.flags_reserved = p->flags & (HRT_RENDER_DEFOCUS | HRT_RENDER_RR);
     h.t_min = p->t_min > 0 ? p->t_min : 0.001f;
-    h.seed = p->seed; h.camera_hash = fnv1a(cam, sizeof(*cam)); h.prim_count = (uint64_t)s->host.n_prims;
+    h.seed = p->seed; h.camera_hash = fnv1a(cam, sizeof(*cam)); h.prim_count = (uint64_t)s->host.n_prims; h.scene_hash = s->host.content_hash;
     return h;
 }
 bool same_render(const CheckpointHeader& a, const CheckpointHeader& b)
 {
     return memcmp(a.magic, b.magic, 8) == 0 && a.width == b.width && a.height == b.height && a.spp == b.spp && a.max_depth == b.max_depth &&
-           a.rng_mode == b.rng_mode && a.flags_reserved == b.flags_reserved && memcmp(&a.t_min, &b.t_min, 4) == 0 && a.seed == b.seed && a.camera_hash == b.camera_hash && a.prim_count == b.prim_count;
+           a.rng_mode == b.rng_mode && a.flags_reserved == b.flags_reserved && memcmp(&a.t_min, &b.t_min, 4) == 0 && a.seed == b.seed && a.camera_hash == b.camera_hash && a.prim_count == b.prim_count && a.scene_hash == b.scene_hash;
 }
 int read_header(const char* path, CheckpointHeader& h, FILE** keep_open)
 {

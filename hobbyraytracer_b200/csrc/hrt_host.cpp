@@ -673,11 +673,51 @@ void build_mesh_host(HostShape& sh, int bvh_mode, uint64_t seed, int shape_id, i
     sh.n_ref_nodes = sh.ref.nodes.size() / 2; sh.n_fast_nodes = sh.fast.nodes.size() / 4; sh.n_leaves = sh.leaves.size() / 8; sh.n_wide_nodes = sh.wide.nodes.size();
 }
 
+// FNV-1a over the scene description.  Arrays above 64 KiB contribute their size and 4096 evenly spaced 16-byte blocks: the hash guards a
+// checkpoint against being resumed on an EDITED scene (hrt_render_progressive), it is not a checksum of every texel.
+namespace {
+struct Fnv {
+    uint64_t h = 1469598103934665603ull;
+    void bytes(const void* p, size_t n) { const unsigned char* b = (const unsigned char*)p; for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 1099511628211ull; } }
+    template <class T> void pod(const T& v) { bytes(&v, sizeof(T)); }
+    void array(const void* p, size_t n)
+    {
+        pod(n);
+        if (!p || n == 0) return;
+        if (n <= (size_t(64) << 10)) { bytes(p, n); return; }
+        const size_t blocks = 4096, step = (n - 16) / (blocks - 1);
+        for (size_t k = 0; k < blocks; ++k) bytes((const unsigned char*)p + k * step, 16);
+    }
+};
+uint64_t scene_content_hash(const HostScene& s)
+{
+    Fnv f;
+    f.pod(s.background); f.pod(s.bvh_mode); f.pod(s.n_prims);
+    for (const HostTexture& t : s.textures) {
+        f.pod(t.kind); f.bytes(t.rgb, sizeof(t.rgb)); f.pod(t.even); f.pod(t.odd); f.pod(t.w); f.pod(t.h); f.pod(t.ch);
+        f.array(t.u8.data(), t.u8.size()); f.array(t.f32.data(), t.f32.size() * 4); f.array(t.rgbe.data(), t.rgbe.size() * 4);
+    }
+    for (const hrt_material& m : s.materials) { f.pod(m.kind); f.bytes(m.albedo, sizeof(m.albedo)); f.pod(m.albedo_tex); f.pod(m.p0); f.pod(m.p0_tex); f.pod(m.p1); f.pod(m.p1_tex); }
+    for (const HostShape& sh : s.shapes) {
+        f.pod(sh.kind); f.bytes(sh.f, sizeof(sh.f)); f.pod(sh.axis); f.pod(sh.material); f.pod(sh.n_tri); f.pod(sh.n_vert);
+        if (sh.indexed) { f.array(sh.V(), (size_t)sh.n_vert * 12); f.array(sh.N(), (size_t)sh.n_vert * 12); f.array(sh.T(), (size_t)sh.n_vert * 8); f.array(sh.I(), (size_t)sh.n_tri * 12); }
+        else { f.array(sh.pos.data(), sh.pos.size() * 4); f.array(sh.nrm.data(), sh.nrm.size() * 4); f.array(sh.uv.data(), sh.uv.size() * 4); }
+    }
+    for (const HostObject& o : s.objects) {
+        f.pod(o.shape); f.pod(o.medium); f.pod(o.neg_inv_density); f.pod(o.phase_tex); f.bytes(o.phase_rgb, sizeof(o.phase_rgb));
+        for (const DXform& x : o.ops) f.bytes(&x, sizeof(DXform));
+    }
+    return f.h;
+}
+} // namespace
+
 std::string flatten(HostScene& s, int bvh_mode, uint64_t seed)
 {
+    s.content_hash = 0;
     const bool fast = bvh_mode != HRT_BVH_REFERENCE;
     int nt = (int)std::thread::hardware_concurrency(); if (nt < 1) nt = 1;
     s.bvh_mode = bvh_mode;
+    s.content_hash = scene_content_hash(s);      // while every source array is still there (borrowed meshes are dropped after the commit)
     s.d_objects.clear(); s.d_xforms.clear(); s.mesh_shapes.clear();
     s.build_ms_ref = s.build_ms_fast = 0;
     for (HostShape& sh : s.shapes) { sh.used = false; sh.mesh_index = -1; }

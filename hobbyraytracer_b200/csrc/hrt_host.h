@@ -114,6 +114,7 @@ struct HostScene {
     float bounds_lo[3] = {0, 0, 0}, bounds_hi[3] = {0, 0, 0};   // union of the world-list entries' padded bounds
     bool has_bounds = false;         // false: some entry is unbounded (or reference-order scene)
     double build_ms_ref = 0, build_ms_fast = 0;
+    uint64_t content_hash = 0;       // of everything that decides the image (flatten(): objects, wrappers, materials, textures, geometry; large arrays sampled): checkpoints carry it
 };
 
 // Converts the ABI's hrt_xform (incl. the *_DEG conveniences) into the device record, with the host-side

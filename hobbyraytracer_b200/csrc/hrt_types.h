@@ -105,7 +105,7 @@ struct DScene {
     int fast;                   // 0: reference visiting order everywhere; 1: SAH BVHs + reference-order re-trace of ambiguous rays
     int big_mesh;               // 1: some mesh has >= 2^17 triangles (its trees leave L1: the wide walk pays for every ray kind)
     int wide_phase_min;         // wide walk: a phase runs when at least this many lanes wait for it (hrt_wide.cuh; 8 with meshes, 16 without)
-    int wide_phase_min_obj;     // the same for the world-list phases (mesh entry, other entries)
+    int wide_phase_min_obj;     // the same for world-list entries that are tested on the spot (spheres, rects, boxes, media)
     int wide_refill;            // wide walk: idle lanes take new rays as soon as fewer than this many lanes are walking (24)
     int refill_secondary;       // 1: secondary rays are traced by the per-lane-refill pass (scenes with meshes: long, uneven walks)
     float tlas_cull_scale;      // lower bound of (reported t) / (world t * |d|) over RotateQuat objects; 0 if none

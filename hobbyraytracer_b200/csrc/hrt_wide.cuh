@@ -421,7 +421,7 @@ __device__ __forceinline__ bool wide_round(WideLane& L, const DScene& s, St& st,
     bool pop = false;
     if (n_in >= thr || n_in == most) { if (w_in) { wide_node_step(L); pop = true; } }
     if (n_tl >= thr || n_tl == most) { if (w_tl) { wide_leaf_step(L); pop = true; } }
-    if (n_me >= thr_ob || n_me == most) { if (w_me) pop = wide_mesh_step(L, s, st); }
+    if (n_me >= thr || n_me == most) { if (w_me) pop = wide_mesh_step(L, s, st); }        // (a mesh entry that waits keeps a long walk from starting: r3i)
     if (n_ob >= thr_ob || n_ob == most) { if (w_ob) { wide_object_step(L, s, key, bounce); pop = true; } }
     if (pop) wide_pop(L, s, st);
     return true;

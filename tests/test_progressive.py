@@ -74,3 +74,24 @@ def test_a_checkpoint_of_another_render_is_refused(scene, tmp_path):
         f.truncate(os.path.getsize(ck) // 2)
     with pytest.raises(abi.HrtError, match="truncated"):
         sc.render_progressive(cam, W, H, SPP, seed=4, checkpoint=ck)
+
+
+@pytest.mark.gpu
+def test_a_checkpoint_of_an_edited_scene_is_refused(hrt, tmp_path):
+    """Same primitive count, same camera, same parameters - but one albedo differs: the checkpoint carries a hash of the scene's content
+    (objects, wrappers, materials, textures, geometry), so the edited scene does not resume into the other one's film."""
+    def build(albedo):
+        sd = abi.SceneDesc()
+        sd.add(sd.sphere((0, 0, -1), 0.5, sd.material(abi.MAT_LAMBERTIAN, albedo)))
+        sd.add(sd.sphere((0, -100.5, -1), 100, sd.material(abi.MAT_LAMBERTIAN, (0.8, 0.8, 0.0))))
+        sd.background = sd.solid((0.6, 0.7, 0.9))
+        return sd.build(hrt, abi.BVH_SAH, 3)
+    cam = scenes.camera_for(dict(position=(0, 0, 0), look_at=(0, 0, -1), up=(0, 1, 0), vfov_deg=60, focal_distance=1.0), 64, 48)
+    ck = str(tmp_path / "film.ckpt")
+    a = build((0.7, 0.3, 0.3))
+    a.render_progressive(cam, 64, 48, 8, seed=2, checkpoint=ck, slice_spp=4)
+    with pytest.raises(abi.HrtError, match="different render"):
+        build((0.3, 0.7, 0.3)).render_progressive(cam, 64, 48, 8, seed=2, checkpoint=ck, slice_spp=4)
+    _, s2, _ = build((0.7, 0.3, 0.3)).render_progressive(cam, 64, 48, 8, seed=2, checkpoint=ck, slice_spp=4)   # the same scene built again resumes
+    s1, _ = a.render(cam, 64, 48, 8, seed=2)
+    assert np.array_equal(s1.view(np.uint32), s2.view(np.uint32))

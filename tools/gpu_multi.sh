@@ -11,7 +11,7 @@ run() { name=$1; shift; P=$((P+1))
   python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $P bench.py --gpus $N "$@" > $O/${TAG}_${name}_${N}gpu.json 2> $O/${TAG}_${name}_${N}gpu.err || tail -c 400 $O/${TAG}_${name}_${N}gpu.err; }
 run shiny_teapot --steps 3 --warmup 3
 run teapot_scene --workload teapot_scene --no-cpu --steps 3 --warmup 3
-run scattered_balls --workload scattered_balls --no-cpu --steps 3 --warmup 3
+[ -z "$SKIP_C3" ] && run scattered_balls --workload scattered_balls --no-cpu --steps 3 --warmup 3
 run cornell_smoke --workload cornell_smoke --no-cpu --steps 2 --warmup 3 --e2e-steps 1
 run big_mesh_lbvh --workload big_mesh --bvh lbvh_gpu --indexed --no-cpu --steps 3 --warmup 3
 run raybatch --workload raybatch --bvh lbvh_gpu --no-cpu --steps 3 --warmup 3

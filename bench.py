@@ -342,7 +342,7 @@ def run_own(args):
                 "samples_per_s": paths / (ms * 1e-3), "samples_per_s_per_gpu": paths / (ms * 1e-3) / world, "rays_per_sample": rays / max(paths, 1),
                 "config": {"workload": f"{info['name']} {w}x{h}, {spp} spp split over {world} GPU(s)", "width": w, "height": h, "spp": spp, "max_depth": 50,
                            "bvh": args.bvh, "n_prims": n_prims, "film_reduce": reduce_kind, "pipeline": "megakernel" if args.megakernel else ("persistent wavefront, every ray queued" if args.pipeline == "v1" else "wavefront, camera paths fused into the trace pass"),
-                           "cache": "camera paths are generated on the device every step (nothing to reuse); between steps the 66 MB film is re-zeroed and the 600 MB of queues rewritten, both larger than L2 with the 33 MB scene; no flush needed"},
+                           "cache": "camera paths are generated on the device every step (nothing to reuse); between steps the film (32 B per pixel) is re-zeroed and the ray queues (up to 5 GB) rewritten, both larger than L2 with the 33 MB scene; no flush needed"},
                 "e2e": {"value": float(e2e_r.item()) / float(e2e_s.item()) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": scene_bytes,
                         "d2h_bytes_per_step": npix * 15, "steps": e2e_steps, "includes": "scene build + BVH build + upload, render, float film + 8-bit image read-back; steps pipelined two deep (a builder thread commits the scene of step k + 1 while step k renders)"},
                 "gpu_launches": int(launches), "commit_s": t_commit, "build_ms": st.ms_build, "replayed_fraction": float(st.retraced) / max(float(st.rays), 1.0), "ref_walk_rays": int(st.prim_tests),

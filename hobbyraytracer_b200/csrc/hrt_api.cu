@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <algorithm>
 #include <atomic>
 #include <mutex>
 #include <unordered_map>
@@ -42,7 +43,13 @@ std::atomic<bool> g_last_secondary_heavy{false};      // kernel choice of the la
 struct BlockCache {
     struct Block { int device; size_t bytes; void* p; };
     std::mutex m; std::vector<Block> blocks; size_t total = 0;
-    static constexpr size_t MAX_TOTAL = size_t(32) << 30, MAX_BLOCKS = 1024;     // C5: 2.9 GB of scene + 1 GB of builder scratch per scene in flight
+    static constexpr size_t MAX_BLOCKS = 1024;
+    size_t MAX_TOTAL = 0;                                   // a quarter of the device's memory, at most 32 GiB (C5: 2.9 GB of scene + 1 GB of builder scratch per scene in flight)
+    size_t limit()
+    {
+        if (!MAX_TOTAL) { size_t fr = 0, tot = 0; MAX_TOTAL = (cudaMemGetInfo(&fr, &tot) == cudaSuccess && tot) ? std::min(tot / 4, size_t(32) << 30) : (size_t(1) << 30); }
+        return MAX_TOTAL;
+    }
     void* take(int device, size_t bytes)
     {
         std::lock_guard<std::mutex> lock(m);
@@ -54,7 +61,7 @@ struct BlockCache {
     {
         {
             std::lock_guard<std::mutex> lock(m);
-            if (blocks.size() < MAX_BLOCKS && total + bytes <= MAX_TOTAL) { blocks.push_back(Block{device, bytes, p}); total += bytes; return; }
+            if (blocks.size() < MAX_BLOCKS && total + bytes <= limit()) { blocks.push_back(Block{device, bytes, p}); total += bytes; return; }
         }
         cudaFree(p);
     }
@@ -114,6 +121,8 @@ struct hrt_scene {
     DScene d{};
     int device = 0, sm_count = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t tb_copy_in = nullptr, tb_copy_out = nullptr;   // hrt_trace_batch on large host batches: copies overlap the walks
+    std::vector<cudaEvent_t> tb_events;
     std::vector<void*> scene_allocs;
     std::unordered_map<void*, size_t> scene_alloc_bytes;        // sizes of the scene's pool blocks (uploads and device-built arrays)
     size_t scene_bytes = 0, h2d_bytes = 0; double ms_build_upload = 0;
@@ -464,6 +473,8 @@ void hrt_scene_destroy(hrt_scene* s)
         cudaFree(s->d_film); cudaFree(s->d_out); cudaFree(s->d_counter);
         if (s->h_ctl) cudaFreeHost(s->h_ctl);
         for (cudaEvent_t e : s->events) cudaEventDestroy(e);
+        if (s->tb_copy_in) { cudaStreamDestroy(s->tb_copy_in); cudaStreamDestroy(s->tb_copy_out); }
+        for (cudaEvent_t e : s->tb_events) cudaEventDestroy(e);
         if (s->stream) cudaStreamDestroy(s->stream);
         if (s->is_replica) cudaSetDevice(cur_dev);
     }
@@ -607,6 +618,33 @@ int hrt_trace_batch(hrt_scene* s, const float* rays, int64_t n, uint32_t* prim_i
     CK(cudaSetDevice(s->device));
     int rc = ensure_tb(s, n, true); if (rc < 0) return rc;
     cudaStream_t st = s->stream;
+    // Large batches in chunks on three streams: chunk c + 1 crosses PCIe while chunk c is walked and the answers of chunk c - 1 go back
+    // (16 Mi rays from pinned memory: 512 MB in, 128 MB out; B200: 23 ms serial).  Only where chunking cannot change an answer: the Philox
+    // key of a ray is its index in the LAUNCH, which matters to ConstantMedium::hit alone (scenes with media take the one-launch path).
+    constexpr int64_t CHUNK = int64_t(2) << 20;
+    bool has_medium = false; for (const HostObject& o : s->host.objects) has_medium |= o.medium;
+    if (n >= 2 * CHUNK && !normal && !uv && !front && !has_medium && !getenv("HRT_TRACE_BATCH_ONE_LAUNCH")) {
+        if (!s->tb_copy_in) { CK(cudaStreamCreateWithFlags(&s->tb_copy_in, cudaStreamNonBlocking)); CK(cudaStreamCreateWithFlags(&s->tb_copy_out, cudaStreamNonBlocking)); }
+        const int n_chunks = (int)((n + CHUNK - 1) / CHUNK);
+        while ((int)s->tb_events.size() < 2 * n_chunks) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); s->tb_events.push_back(e); }
+        CK(cudaStreamSynchronize(st));                                         // earlier work on the scene's stream may still use the buffers
+        for (int c = 0; c < n_chunks; ++c) {
+            const int64_t off = (int64_t)c * CHUNK, m = std::min(CHUNK, n - off);
+            CK(cudaMemcpyAsync(s->tb_rays + 2 * off, rays + 8 * off, sizeof(float) * 8 * (size_t)m, cudaMemcpyHostToDevice, s->tb_copy_in));
+            CK(cudaEventRecord(s->tb_events[2 * c], s->tb_copy_in));
+            CK(cudaStreamWaitEvent(st, s->tb_events[2 * c], 0));
+            launch_trace_batch(s->d, s->tb_rays + 2 * off, m, s->tb_hits, rng_seed, s->d_counter, s->tb_pend, s->tb_pend + n, s->sm_count, st, &s->stats.launches);
+            launch_split_hits(s->tb_hits, m, s->tb_prim + off, s->tb_t + off, s->sm_count, st, &s->stats.launches);
+            CK(cudaEventRecord(s->tb_events[2 * c + 1], st));
+            CK(cudaStreamWaitEvent(s->tb_copy_out, s->tb_events[2 * c + 1], 0));
+            CK(cudaMemcpyAsync(prim_id + off, s->tb_prim + off, sizeof(uint32_t) * (size_t)m, cudaMemcpyDeviceToHost, s->tb_copy_out));
+            CK(cudaMemcpyAsync(t + off, s->tb_t + off, sizeof(float) * (size_t)m, cudaMemcpyDeviceToHost, s->tb_copy_out));
+        }
+        CK(cudaStreamSynchronize(s->tb_copy_out)); CK(cudaStreamSynchronize(st));
+        CK(cudaGetLastError());
+        s->stats.rays += (uint64_t)n;
+        return 0;
+    }
     CK(cudaMemcpyAsync(s->tb_rays, rays, sizeof(float) * 8 * (size_t)n, cudaMemcpyHostToDevice, st));
     rc = hrt_trace_batch_device(s, s->tb_rays, n, s->tb_prim, s->tb_t, rng_seed, st); if (rc < 0) return rc;
     CK(cudaMemcpyAsync(prim_id, s->tb_prim, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToHost, st));

@@ -390,6 +390,22 @@ def test_large_batch_orders_agree(hrt, cache_dir):
     assert (a["prim"] != abi.MISS).mean() > 0.15
 
 
+def test_chunked_host_batch_equals_one_launch(hrt, cache_dir):
+    """hrt_trace_batch on a large host batch runs in chunks on three streams (copies overlap the walks): the answers are those of the
+    one-launch path, bit for bit, including the ragged last chunk."""
+    sd, cam, _ = scenes.shiny_teapot_scene(cache_dir, env_w=64, env_h=32)
+    rays = scenes.random_rays(5 * (1 << 20) + 12345, (0, 0.8, 0), 1.5 * 1.2, seed=21)
+    sc = sd.build(hrt, abi.BVH_SAH, 3)
+    a = sc.trace(rays, extras=False)                                  # >= 4 Mi rays, no extras, no media: chunked
+    os.environ["HRT_TRACE_BATCH_ONE_LAUNCH"] = "1"
+    try:
+        b = sc.trace(rays, extras=False)
+    finally:
+        del os.environ["HRT_TRACE_BATCH_ONE_LAUNCH"]
+    assert np.array_equal(a["prim"], b["prim"]) and np.array_equal(bits(a["t"]), bits(b["t"]))
+    assert sc.stats().rays == 2 * len(rays)
+
+
 @pytest.mark.parametrize("mode", MODES)
 def test_nan_rays(orc, hrt, mode):
     """Rays left behind by NaN-t hits (all-NaN origin: answered without a walk) and partially non-finite rays

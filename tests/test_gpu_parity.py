@@ -390,6 +390,23 @@ def test_large_batch_orders_agree(hrt, cache_dir):
     assert (a["prim"] != abi.MISS).mean() > 0.15
 
 
+def test_full_resolution_wavefront_equals_megakernel(hrt, cache_dir):
+    """BASELINE config 2 at its own resolution (1920 x 1080; 40 spp = 83 M camera paths, more than the 32 Mi queue entries, so the
+    camera-path kernel fills the queues and stops several times): the persistent wavefront and the one-thread-per-path kernel produce the
+    same film bit for bit, nothing is clamped, and the rays-per-sample figure is the one the bench reports (1.10)."""
+    sd, cam, _ = scenes.shiny_teapot_scene(cache_dir, env_w=512, env_h=256)
+    w, h, spp = 1920, 1080, 40
+    c = scenes.camera_for(cam, w, h)
+    g = sd.build(hrt, abi.BVH_SAH, 3)
+    a, img = g.render(c, w, h, spp, seed=77)
+    st = g.stats()
+    b, _ = g.render(c, w, h, spp, seed=77, flags=abi.RENDER_MEGAKERNEL)
+    assert np.array_equal(bits(a), bits(b))
+    assert st.film_clamped == 0 and st.paths == w * h * spp
+    assert 1.05 < st.rays / st.paths < 1.15
+    assert img.shape == (h, w, 3) and img.mean() > 10
+
+
 def test_chunked_host_batch_equals_one_launch(hrt, cache_dir):
     """hrt_trace_batch on a large host batch runs in chunks on three streams (copies overlap the walks): the answers are those of the
     one-launch path, bit for bit, including the ragged last chunk."""

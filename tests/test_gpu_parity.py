@@ -407,6 +407,25 @@ def test_full_resolution_wavefront_equals_megakernel(hrt, cache_dir):
     assert img.shape == (h, w, 3) and img.mean() > 10
 
 
+@pytest.mark.parametrize("name,w,h,spp", [("teapot_scene", 640, 640, 12), ("cornell_smoke", 1024, 1024, 6), ("scattered_balls", 1200, 800, 6)])
+def test_other_configs_at_their_resolution(hrt, cache_dir, name, w, h, spp):
+    """BASELINE configs 1, 4 and 3 at their own resolutions (a few samples per pixel): every pipeline the host picks for them - wide
+    secondary pass with per-scene thresholds, lock-step pass, media inside hit() - gives the megakernel's film bit for bit."""
+    if name == "teapot_scene":
+        sd, cam, _ = scenes.teapot_scene(cache_dir, n=56, env_w=64, env_h=32)
+    elif name == "cornell_smoke":
+        sd, cam = scenes.cornell_smoke_scene()[:2]
+    else:
+        sd, cam = scenes.scattered_balls_scene()[:2]
+    c = scenes.camera_for(cam, w, h)
+    g = sd.build(hrt, abi.BVH_SAH, 3)
+    for rep in range(2):                                   # the second render starts from the kernel choice the first one found
+        a, _ = g.render(c, w, h, spp, seed=5 + rep)
+        assert g.stats().film_clamped == 0
+        b, _ = g.render(c, w, h, spp, seed=5 + rep, flags=abi.RENDER_MEGAKERNEL)
+        assert np.array_equal(bits(a), bits(b)), (name, rep)
+
+
 def test_chunked_host_batch_equals_one_launch(hrt, cache_dir):
     """hrt_trace_batch on a large host batch runs in chunks on three streams (copies overlap the walks): the answers are those of the
     one-launch path, bit for bit, including the ragged last chunk."""

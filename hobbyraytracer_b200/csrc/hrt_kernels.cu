@@ -904,11 +904,12 @@ void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, i
     if (wsec) { k_wide_secondary<<<sm_count * HRT_WSEC_MIN_BLOCKS, BLOCK, 0, st>>>(s, j, it & 1); *launches += 1; }
     const bool lens = cam.lens_radius > 0.0f;
     const int q = it & 1;
+    static const int tb = getenv("HRT_TRACE_BUILD") ? atoi(getenv("HRT_TRACE_BUILD")) : 0;      // A/B: 4 = 128-register build, 8 = 64-register build
     if (s.big_mesh || force_wtrace) {
         const int blocks = wave2_trace_blocks(j.capacity, sm_count, HRT_WTRACE_MIN_BLOCKS);
         if (lens) k_wave2_trace<HRT_WTRACE_MIN_BLOCKS, true, true><<<blocks, BLOCK, 0, st>>>(s, j, cam, q, wsec);
         else k_wave2_trace<HRT_WTRACE_MIN_BLOCKS, false, true><<<blocks, BLOCK, 0, st>>>(s, j, cam, q, wsec);
-    } else if (secondary_heavy) {
+    } else if (tb ? tb == 8 : secondary_heavy) {
         if (lens) k_wave2_trace<8, true, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, q, wsec);
         else k_wave2_trace<8, false, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, q, wsec);
     } else {

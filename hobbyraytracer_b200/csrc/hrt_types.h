@@ -107,7 +107,7 @@ struct DScene {
     int wide_phase_min;         // wide walk: a phase runs when at least this many lanes wait for it (hrt_wide.cuh; 8 with meshes, 16 without)
     int wide_phase_min_obj;     // the same for world-list entries that are tested on the spot (spheres, rects, boxes, media)
     int wide_refill;            // wide walk: idle lanes take new rays as soon as fewer than this many lanes are walking (24)
-    int refill_secondary;       // 1: secondary rays are traced by the per-lane-refill pass (scenes with meshes: long, uneven walks)
+    int refill_secondary;       // 1: when secondary rays dominate they are traced by k_wide_secondary (scenes with meshes, or with at most 64 world-list entries)
     float tlas_cull_scale;      // lower bound of (reported t) / (world t * |d|) over RotateQuat objects; 0 if none
     int has_bounds;             // 1: bounds_lo/hi enclose every world-list entry (camera rays that pass outside are misses)
     float bounds_lo[3], bounds_hi[3];

@@ -216,7 +216,9 @@ int hrt_scene_commit(hrt_scene* s, int bvh_mode, uint64_t seed);
 /* Closest-hit on a ray batch: world->hit(r, t_min, t_max, rec) of main.cpp:45 / hittableList.cpp:4-21.
  * rays: n x 8 floats (ox,oy,oz,t_min, dx,dy,dz,t_max).  Outputs: primitive id (HRT_MISS on miss) and rec.t.
  * optional outputs (may be NULL): normal n x 3 (rec.normal), uv n x 2, front n bytes (rec.frontFace).
- * rng_seed only matters for scenes with media (their hit() draws a random number). */
+ * rng_seed only matters for scenes with media (their hit() draws a random number).
+ * Batches of 4 Mi rays and more without the optional outputs (scenes without media) run in 2 Mi-ray chunks on internal streams, the copies of
+ * one chunk overlapping the walks of another: give pinned host memory to let them overlap; the answers do not depend on the chunking. */
 int hrt_trace_batch(hrt_scene* s, const float* rays, int64_t n, uint32_t* prim_id, float* t,
                     float* normal, float* uv, uint8_t* front, uint64_t rng_seed);
 /* Same with device-resident buffers (inputs already in HBM); stream = cudaStream_t or NULL. */

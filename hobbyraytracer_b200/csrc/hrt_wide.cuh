@@ -361,7 +361,9 @@ struct WideArrayStack {
     HRT_HD void drop() { --sp; }
     HRT_HD bool empty() const { return sp == 0; }
 };
-HRT_HDN inline Hit wide_trace_scalar(const DScene& s, const Ray& r, float t_min, float t_max, const RngKey& key, uint32_t bounce, unsigned long long* steps)
+// kinds (may be NULL): 4 counters - node steps, triangle leaves, mesh entries, other world-list entries (the visit counts behind SURVEY 8(d)'s B_logical)
+HRT_HDN inline Hit wide_trace_scalar(const DScene& s, const Ray& r, float t_min, float t_max, const RngKey& key, uint32_t bounce, unsigned long long* steps,
+                                     unsigned long long* kinds = nullptr)
 {
     WideLane L; Hit h;
     if (!wide_begin(L, s, r, t_min, t_max, h)) {
@@ -371,10 +373,10 @@ HRT_HDN inline Hit wide_trace_scalar(const DScene& s, const Ray& r, float t_min,
         while (L.live) {
             if (steps) ++*steps;
             bool pop = true;
-            if (L.cur >= 0) wide_node_step(L);
-            else if (L.obj >= 0) wide_leaf_step(L);
-            else if ((uint32_t)(~L.cur) & WIDE_MESH_BIT) pop = wide_mesh_step(L, s, st);
-            else wide_object_step(L, s, key, bounce);
+            if (L.cur >= 0) { if (kinds) ++kinds[0]; wide_node_step(L); }
+            else if (L.obj >= 0) { if (kinds) ++kinds[1]; wide_leaf_step(L); }
+            else if ((uint32_t)(~L.cur) & WIDE_MESH_BIT) { if (kinds) ++kinds[2]; pop = wide_mesh_step(L, s, st); }
+            else { if (kinds) ++kinds[3]; wide_object_step(L, s, key, bounce); }
             if (pop) wide_pop(L, s, st);
         }
     }

@@ -120,6 +120,25 @@ int hsim_trace_batch_wide(hsim_scene* s, const float* rays, int64_t n, uint32_t*
     if (out_steps) *out_steps = steps;
     return 0;
 }
+// Visit counts of the wide walk per ray kind of step (node steps, triangle leaves, mesh entries, other world-list entries) and the rays left to
+// pass 2: the figures behind SURVEY 8(d)'s supplementary B_logical (tools/b_logical.py).  out5: the four counters + pending rays.
+int hsim_wide_visit_counts(hsim_scene* s, const float* rays, int64_t n, uint64_t rng_seed, uint64_t* out5)
+{
+    if (!s->host.committed) { g_err = "scene not committed"; return HRT_ERR_STATE; }
+    if (!s->d.wide) { g_err = "scene has no wide trees"; return HRT_ERR_STATE; }
+    std::atomic<unsigned long long> k0(0), k1(0), k2(0), k3(0), pend(0);
+    parallel_for(n, 4096, [&](int64_t i) {
+        const float* q = rays + i * 8;
+        Ray r; r.o = v3(q[0], q[1], q[2]); r.d = v3(q[4], q[5], q[6]);
+        RngKey key; key.k0 = (uint32_t)rng_seed; key.k1 = (uint32_t)(rng_seed >> 32); key.index = (uint32_t)i; key.sample = (uint32_t)(i >> 32); key.mode = 0;
+        unsigned long long st = 0, kinds[4] = {0, 0, 0, 0};
+        Hit h = wide_trace_scalar(s->d, r, q[3], q[7], key, 0, &st, kinds);
+        k0 += kinds[0]; k1 += kinds[1]; k2 += kinds[2]; k3 += kinds[3];
+        if (h.flags & (HIT_RESOLVED | HIT_FALLBACK)) pend += 1;
+    });
+    out5[0] = k0; out5[1] = k1; out5[2] = k2; out5[3] = k3; out5[4] = pend;
+    return 0;
+}
 // Texture::colourValue through the device header on the flattened scene (exercises the lossless RGBE repack of env maps)
 int hsim_texture_eval(hsim_scene* s, int tex, const float* in, int64_t n, float* out)
 {

@@ -169,3 +169,17 @@ def test_wide_collapse_structure(hsim, mode):
         assert (lo[i, :, s] <= blo).all() and (hi[i, :, s] >= bhi).all(), (i, s, c)
         sub_lo[i] = np.minimum(sub_lo[i], blo); sub_hi[i] = np.maximum(sub_hi[i], bhi)
         assert (hi[i, :, s] - lo[i, :, s] <= (bhi - blo) + 2.0 * step[i] + 1e-30).all(), "quantisation adds at most one grid step per side"
+
+
+def test_visit_counts_by_kind_add_up(hsim):
+    """hsim_wide_visit_counts (the figures behind tools/b_logical.py): node steps + triangle leaves + mesh entries + other entries = the steps
+    trace_batch_wide reports; a scene with one mesh enters it at most once per ray."""
+    sc = mesh_scene(24).build(hsim, abi.BVH_SAH, 9)
+    rays = np.ascontiguousarray(scenes.random_rays(20000, (0, 1, 0), 2.5, seed=4), F)
+    f = hsim.dll.hsim_wide_visit_counts
+    f.restype = C.c_int; f.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_uint64, C.c_void_p]
+    out = (C.c_uint64 * 5)()
+    assert f(sc.h, rays.ctypes.data, len(rays), 0, out) == 0
+    node, leaf, mesh, entry, pend = list(out)
+    assert node + leaf + mesh + entry == wide_trace(hsim, sc, rays)["steps"]
+    assert 0 < mesh <= len(rays) and node > leaf > 0 and pend < len(rays) // 10

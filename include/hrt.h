@@ -252,7 +252,10 @@ int hrt_scatter_batch(hrt_scene* s, int material, const float* in14, const uint8
 
 /* render(): main.cpp:81-140.  out_sum: width*height*3 floats receiving the per-pixel *sum* of the rendered
  * samples (NULL to skip); out_rgb8: width*height*3 bytes = Film::tonemap + writeColour of sum/spp
- * (film.cpp:25-52), row 0 = top row as in the reference's pixel buffer (NULL to skip). */
+ * (film.cpp:25-52), row 0 = top row as in the reference's pixel buffer (NULL to skip).
+ * Device memory besides the scene: the integer film (32 B per pixel) and the ray queues of the wavefront, 148 B per entry for
+ * min(32 Mi, camera paths of the call) entries (at most ~5 GB; HRT_WAVE_CAPACITY overrides the entry count); both are kept for the next
+ * render and for the next scene of the process (hrt_trim releases them). */
 int hrt_render(hrt_scene* s, const hrt_camera* cam, const hrt_render_params* p, float* out_sum, uint8_t* out_rgb8);
 /* render() in slices, with checkpoints and the reference's progress reporting (main.cpp:95-109 prints "Pixels rendered"
  * from a reporter thread; here the caller gets a callback after every slice).  The p->spp samples of every pixel are

@@ -784,7 +784,9 @@ std::string flatten(HostScene& s, int bvh_mode, uint64_t seed)
         auto mark = [&](int32_t c) -> int32_t {
             if (c >= 0) return c;
             const DObject& ob = s.d_objects[(size_t)(~c)];
-            return (ob.kind == SHAPE_MESH && !ob.medium) ? (int32_t)~((uint32_t)(~c) | (1u << 30)) : c;
+            if (ob.kind == SHAPE_MESH && !ob.medium) return (int32_t)~((uint32_t)(~c) | (1u << 30));        // WIDE_MESH_BIT
+            const bool plain = !ob.medium && ob.xf_count == 0 && (ob.kind == SHAPE_SPHERE || ob.kind == SHAPE_RECT);
+            return plain ? c : (int32_t)~((uint32_t)(~c) | (1u << 29));                                     // WIDE_SLOW_BIT
         };
         for (WNode& n : s.tlas_wide.nodes)
             for (int k = 0; k < 8; ++k) if ((n.meta >> (24 + k)) & 1u) n.child[k] = mark(n.child[k]);

@@ -28,6 +28,9 @@ constexpr int WIDE_STACK = 32;                        // stack entries per lane 
 constexpr float WIDE_WIDEN = 9.5367431640625e-7f;     // 2^-20, relative to |(p - o) / d| + |grid extent / d| (see wide_hits)
 constexpr int HIT_PENDING = 8;                        // Hit::flags: pass 1 could not decide; Hit::t carries the cull bound
 constexpr int PEND_BAD = 16, PEND_SHEAR = 32;         // Hit::flags of a pending entry: arguments of trace_resolve
+constexpr uint32_t WIDE_SLOW_BIT = 1u << 29;          // top-level leaf: an entry that takes the general, out-of-line object test (wrapped shapes, boxes, media):
+                                                      // those lanes get a phase of their own, so the large cold function runs for many lanes at a time
+constexpr uint32_t WIDE_TAG_BITS = (1u << 30) | (1u << 29);
 constexpr uint32_t WIDE_MESH_BIT = 1u << 30;          // top-level leaf ~(entry | WIDE_MESH_BIT): the entry is a mesh that gets ENTERED (no medium),
                                                       // so a warp can tell the lanes that wait for a mesh entry from those that wait for
                                                       // a sphere / rect / box / medium test without a load (set by flatten(), hrt_host.cpp)
@@ -295,7 +298,7 @@ HRT_HD void wide_leaf_step(WideLane& L)
 // mesh was NOT entered (empty mesh, or a ray pass 2 has to take: L.b.bad / L.b.shear) and the lane pops instead.
 template <class St> HRT_HD bool wide_mesh_step(WideLane& L, const DScene& s, St& st)
 {
-    const int i = (int)((uint32_t)(~L.cur) & ~WIDE_MESH_BIT);
+    const int i = (int)((uint32_t)(~L.cur) & ~WIDE_TAG_BITS);
     const DObject& ob = s.objects[i];
     const DMesh& m = s.meshes[ob.mesh];
     L.cur = 0;
@@ -318,21 +321,22 @@ template <class St> HRT_HD bool wide_mesh_step(WideLane& L, const DScene& s, St&
     return false;
 }
 
-// ---- any other world-list entry (sphere, rect, box, medium ...): tested on the spot
+// ---- any other world-list entry: tested on the spot.  SLOW = false: the entries without WIDE_SLOW_BIT (plain spheres and rects, in line);
+// SLOW = true: everything else through the general object test (out of line)
 // (one entry per call: taking a lane's next entries in the same call - a Cornell-box ray holds three in a row - was slower,
 // teapot_scene 1612 -> 1496 Mrays/s, and unrolled it outgrew the instruction cache: 931, profiles/README.md r2h / r2i)
+template <bool SLOW>
 HRT_HD void wide_object_step(WideLane& L, const DScene& s, const RngKey& key, uint32_t bounce)
 {
-    const int i = (int)((uint32_t)(~L.cur) & ~WIDE_MESH_BIT);
+    const int i = (int)((uint32_t)(~L.cur) & ~WIDE_TAG_BITS);
     const DObject& ob = s.objects[i];
     float t = 0.0f; uint32_t prim = ob.prim_base; bool hit;
     const float bound = cull_bound(L.b);
-    if (!ob.medium && ob.xf_count == 0 && ob.kind == SHAPE_SPHERE) hit = sphere_t(ob.f, L.r, L.t_min, bound, t);    // the common entries in line
-    else if (!ob.medium && ob.xf_count == 0 && ob.kind == SHAPE_RECT) { float a, b; hit = rect_t(ob.axis, ob.f[0], ob.f[1], ob.f[2], ob.f[3], ob.f[4], L.r, L.t_min, bound, t, a, b); }
-    else {
+    if (SLOW) {
         const Ray wr = L.r;                                             // a copy: hit_object_ref is out of line
         hit = hit_object_ref(s, i, wr, L.t_min, bound, t, prim, key, bounce);
-    }
+    } else if (ob.kind == SHAPE_SPHERE) hit = sphere_t(ob.f, L.r, L.t_min, bound, t);
+    else { float a, b; hit = rect_t(ob.axis, ob.f[0], ob.f[1], ob.f[2], ob.f[3], ob.f[4], L.r, L.t_min, bound, t, a, b); }
     if (hit) { consider(L.b, t, t, prim, i); wide_set_bound(L); }
     L.cur = 0;
 }
@@ -376,7 +380,8 @@ HRT_HDN inline Hit wide_trace_scalar(const DScene& s, const Ray& r, float t_min,
             if (L.cur >= 0) { if (kinds) ++kinds[0]; wide_node_step(L); }
             else if (L.obj >= 0) { if (kinds) ++kinds[1]; wide_leaf_step(L); }
             else if ((uint32_t)(~L.cur) & WIDE_MESH_BIT) { if (kinds) ++kinds[2]; pop = wide_mesh_step(L, s, st); }
-            else { if (kinds) ++kinds[3]; wide_object_step(L, s, key, bounce); }
+            else if ((uint32_t)(~L.cur) & WIDE_SLOW_BIT) { if (kinds) ++kinds[3]; wide_object_step<true>(L, s, key, bounce); }
+            else { if (kinds) ++kinds[3]; wide_object_step<false>(L, s, key, bounce); }
             if (pop) wide_pop(L, s, st);
         }
     }
@@ -409,14 +414,18 @@ template <class St>
 __device__ __forceinline__ bool wide_round(WideLane& L, const DScene& s, St& st, const RngKey& key, uint32_t bounce)
 {
     const bool top_leaf = L.live && L.cur < 0 && L.obj < 0;
-    const bool is_mesh = ((uint32_t)(~L.cur) & WIDE_MESH_BIT) != 0u;
+    const uint32_t tag = (uint32_t)(~L.cur) & WIDE_TAG_BITS;
     const bool w_in = L.live && L.cur >= 0;
     const bool w_tl = L.live && L.cur < 0 && L.obj >= 0;
-    const bool w_me = top_leaf && is_mesh;
-    const bool w_ob = top_leaf && !is_mesh;
+    const bool w_me = top_leaf && tag == WIDE_MESH_BIT;
+    const bool w_ob = top_leaf && tag == 0u;
+    const bool w_sl = top_leaf && tag == WIDE_SLOW_BIT;
     const int n_in = __popc(__ballot_sync(0xffffffffu, w_in)), n_tl = __popc(__ballot_sync(0xffffffffu, w_tl));
-    const int n_me = __popc(__ballot_sync(0xffffffffu, w_me)), n_ob = __popc(__ballot_sync(0xffffffffu, w_ob));
-    const int most = max(max(n_in, n_tl), max(n_me, n_ob));
+    int n_me = 0, n_ob = 0, n_sl = 0;
+    if (__ballot_sync(0xffffffffu, top_leaf)) {                                // warp-uniform: inside a large mesh most rounds have no lane at the top level
+        n_me = __popc(__ballot_sync(0xffffffffu, w_me)); n_ob = __popc(__ballot_sync(0xffffffffu, w_ob)); n_sl = __popc(__ballot_sync(0xffffffffu, w_sl));
+    }
+    const int most = max(max(max(n_in, n_tl), max(n_me, n_ob)), n_sl);
     if (most == 0) return false;
     // a phase runs when enough lanes wait for it, or when no phase has more (the largest group always runs: progress)
     const int thr = s.wide_phase_min, thr_ob = s.wide_phase_min_obj;
@@ -424,7 +433,8 @@ __device__ __forceinline__ bool wide_round(WideLane& L, const DScene& s, St& st,
     if (n_in >= thr || n_in == most) { if (w_in) { wide_node_step(L); pop = true; } }
     if (n_tl >= thr || n_tl == most) { if (w_tl) { wide_leaf_step(L); pop = true; } }
     if (n_me >= thr || n_me == most) { if (w_me) pop = wide_mesh_step(L, s, st); }        // (a mesh entry that waits keeps a long walk from starting: r3i)
-    if (n_ob >= thr_ob || n_ob == most) { if (w_ob) { wide_object_step(L, s, key, bounce); pop = true; } }
+    if (n_ob >= thr_ob || n_ob == most) { if (w_ob) { wide_object_step<false>(L, s, key, bounce); pop = true; } }
+    if (n_sl >= thr_ob || n_sl == most) { if (w_sl) { wide_object_step<true>(L, s, key, bounce); pop = true; } }
     if (pop) wide_pop(L, s, st);
     return true;
 }

@@ -1013,7 +1013,7 @@ int make_replica(hrt_scene* s, int device, hrt_scene** out)
     DevUp up(r->scene_allocs, r->scene_alloc_bytes, device);
     up.dev_override = &r->dev_meshes;
     r->d = make_dscene(s->host, up);
-    r->d.refill_secondary = s->d.refill_secondary; r->d.wide_phase_min = s->d.wide_phase_min; r->d.wide_phase_min_obj = s->d.wide_phase_min_obj; r->d.wide_refill = s->d.wide_refill;
+    r->d.refill_secondary = s->d.refill_secondary; r->d.wide_has_slow = s->d.wide_has_slow; r->d.wide_phase_min = s->d.wide_phase_min; r->d.wide_phase_min_obj = s->d.wide_phase_min_obj; r->d.wide_refill = s->d.wide_refill;
     if (up.failed) return fail("replica upload failed: " + up.msg);
     r->scene_bytes += up.bytes;
     e = cudaDeviceSynchronize();

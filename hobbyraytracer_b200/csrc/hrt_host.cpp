@@ -774,7 +774,7 @@ std::string flatten(HostScene& s, int bvh_mode, uint64_t seed)
         }
     }
     s.tlas_cull_scale = any_quat ? cull_scale : 0.0f;
-    s.tlas = FastBvh(); s.tlas_wide = WideBvh(); s.has_bounds = false;
+    s.tlas = FastBvh(); s.tlas_wide = WideBvh(); s.has_bounds = false; s.tlas_has_slow = false;
     if (fast && !s.objects.empty()) {
         // float(double) may round inwards by half an ulp: push the bounds one step outwards
         for (size_t k = 0; k < obmin.size(); ++k) { obmin[k] = std::nextafter(obmin[k], -std::numeric_limits<float>::infinity()); obmax[k] = std::nextafter(obmax[k], std::numeric_limits<float>::infinity()); }
@@ -786,6 +786,7 @@ std::string flatten(HostScene& s, int bvh_mode, uint64_t seed)
             const DObject& ob = s.d_objects[(size_t)(~c)];
             if (ob.kind == SHAPE_MESH && !ob.medium) return (int32_t)~((uint32_t)(~c) | (1u << 30));        // WIDE_MESH_BIT
             const bool plain = !ob.medium && ob.xf_count == 0 && (ob.kind == SHAPE_SPHERE || ob.kind == SHAPE_RECT);
+            if (!plain) s.tlas_has_slow = true;
             return plain ? c : (int32_t)~((uint32_t)(~c) | (1u << 29));                                     // WIDE_SLOW_BIT
         };
         for (WNode& n : s.tlas_wide.nodes)

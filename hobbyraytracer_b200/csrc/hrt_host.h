@@ -110,6 +110,7 @@ struct HostScene {
     std::vector<int> mesh_shapes;    // DScene::meshes[i] is built from shapes[mesh_shapes[i]]
     FastBvh tlas;
     WideBvh tlas_wide;
+    bool tlas_has_slow = false;      // some top-level leaf of tlas_wide is tagged WIDE_SLOW_BIT (hrt_wide.cuh)
     float tlas_cull_scale = 1.0f;
     float bounds_lo[3] = {0, 0, 0}, bounds_hi[3] = {0, 0, 0};   // union of the world-list entries' padded bounds
     bool has_bounds = false;         // false: some entry is unbounded (or reference-order scene)

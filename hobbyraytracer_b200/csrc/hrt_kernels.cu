@@ -74,6 +74,7 @@ __global__ void __launch_bounds__(BLOCK) k_trace_batch_plain(DScene s, const flo
         hits[i] = s.fast ? trace_fast<false>(s, r, a.w, b.w, key, 0, nullptr) : trace_ref(s, r, a.w, b.w, key, 0);
     }
 }
+template <bool SLOW>
 __global__ void __launch_bounds__(BLOCK, HRT_BATCH_MIN_BLOCKS) k_trace_batch(DScene s, const float4* __restrict__ rays, long long n, Hit* __restrict__ hits, uint64_t seed,
                                                                             unsigned long long* __restrict__ counter, PendList pend)
 {
@@ -112,7 +113,7 @@ __global__ void __launch_bounds__(BLOCK, HRT_BATCH_MIN_BLOCKS) k_trace_batch(DSc
             }
         }
         const RngKey key = make_key(seed, (uint32_t)idx, (uint32_t)((unsigned long long)idx >> 32), 0);
-        if (!wide_round(L, s, st, key, 0) && exhausted) {
+        if (!wide_round<WideSmemStack<BLOCK>, SLOW>(L, s, st, key, 0) && exhausted) {
             if (!__any_sync(0xffffffffu, idx >= 0)) break;
         }
     }
@@ -515,7 +516,7 @@ __device__ __forceinline__ bool camera_ray_clears_scene(const DScene& s, const R
 // WIDE: the walks of a step of the warp (32 entries, or the 32 camera rays of one sample of the claim) go through the 8-wide trees
 // together, in phases (hrt_wide.cuh, no refill: the claim structure stays); used on scenes with large meshes, where the
 // two-child walk is a chain of ~50 dependent fetches per ray.
-template <int MINB, bool LENS, bool WIDE>
+template <int MINB, bool LENS, bool WIDE, bool SLOW = true>
 __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j, DCamera cam, int q, int skip_secondary)
 {
     __shared__ int stack_mem[WIDE ? WIDE_STACK * BLOCK : 1];
@@ -583,7 +584,7 @@ __global__ void __launch_bounds__(BLOCK, MINB) k_wave2_trace(DScene s, WaveJob j
             WideLane L; L.live = false; L.b.bad = 0;
             bool began = false;
             if (walk) began = wide_begin(L, s, r, j.t_min, hrt_inf(), h);
-            while (wide_round(L, s, stk, key, st & 0xffu)) { }
+            while (wide_round<WideSmemStack<BLOCK>, SLOW>(L, s, stk, key, st & 0xffu)) { }
             if (walk && (began || L.b.bad)) {
                 h = wide_result(L);
                 if (h.flags & HIT_PENDING) h = wide_resolve(s, r, j.t_min, hrt_inf(), key, st & 0xffu, h);
@@ -677,6 +678,7 @@ __global__ void __launch_bounds__(SHADE_BLOCK) k_wave2_shade(DScene s, WaveJob j
 #ifndef HRT_WSEC_MIN_BLOCKS
 #define HRT_WSEC_MIN_BLOCKS 5      // teapot_scene 1501 (4 blocks) / 1611 (5) / 1504 (6) / 1292 (8) Mrays/s (r2f)
 #endif
+template <bool SLOW>
 __global__ void __launch_bounds__(BLOCK, HRT_WSEC_MIN_BLOCKS) k_wide_secondary(DScene s, WaveJob j, int q)
 {
     __shared__ int stack_mem[WIDE_STACK * BLOCK];
@@ -716,7 +718,7 @@ __global__ void __launch_bounds__(BLOCK, HRT_WSEC_MIN_BLOCKS) k_wide_secondary(D
             }
         }
         const RngKey key = make_key(j.seed, (uint32_t)r_pix, (uint32_t)(j.s_first + (int)((r_st >> 8) & 0x7fffffu)), j.rng_mode);
-        if (!wide_round(L, s, st, key, r_st & 0xffu) && exhausted) {
+        if (!wide_round<WideSmemStack<BLOCK>, SLOW>(L, s, st, key, r_st & 0xffu) && exhausted) {
             if (!__any_sync(0xffffffffu, have)) break;
         }
     }
@@ -783,7 +785,8 @@ void launch_trace_batch(const DScene& s, const float4* d_rays, long long n, Hit*
     cudaMemsetAsync(d_pend_count, 0, sizeof(unsigned int), st);
     PendList pend; pend.idx = d_pend_idx; pend.count = d_pend_count; pend.cap = (unsigned int)(n < 0xffffffffll ? n : 0xffffffffll);
     if (!s.wide || getenv("HRT_NO_WIDE")) { k_trace_batch_plain<<<grid_for(n, sm_count, 16), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed); *launches += 1; return; }
-    k_trace_batch<<<grid_for(n, sm_count, HRT_BATCH_MIN_BLOCKS), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed, d_counter, pend);
+    if (s.wide_has_slow) k_trace_batch<true><<<grid_for(n, sm_count, HRT_BATCH_MIN_BLOCKS), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed, d_counter, pend);
+    else k_trace_batch<false><<<grid_for(n, sm_count, HRT_BATCH_MIN_BLOCKS), BLOCK, 0, st>>>(s, d_rays, n, d_hits, seed, d_counter, pend);
     k_resolve_batch<<<sm_count * 8, BLOCK, 0, st>>>(s, d_rays, d_hits, seed, pend); *launches += 2;
 }
 // ---- hrt_trace_batch_static: the ray batch without any allocation -------------------------------------------------------------------
@@ -901,14 +904,19 @@ void launch_wave3_trace(const DScene& s, const WaveJob& j, const DCamera& cam, i
     // pass is as good or better (B200 A/B r2f: shiny_teapot 8874 vs 8658, scattered_balls 5300 vs 3276, cornell_smoke 4070 vs 3626)
     const bool force_wsec = getenv("HRT_FORCE_WIDE_SECONDARY") != nullptr, force_wtrace = getenv("HRT_FORCE_WIDE_PRIMARY") != nullptr;   // tests, sanitizer runs
     const int wsec = ((s.refill_secondary && (secondary_heavy || s.big_mesh)) || force_wsec) ? 1 : 0;
-    if (wsec) { k_wide_secondary<<<sm_count * HRT_WSEC_MIN_BLOCKS, BLOCK, 0, st>>>(s, j, it & 1); *launches += 1; }
+    if (wsec) {
+        if (s.wide_has_slow) k_wide_secondary<true><<<sm_count * HRT_WSEC_MIN_BLOCKS, BLOCK, 0, st>>>(s, j, it & 1);
+        else k_wide_secondary<false><<<sm_count * HRT_WSEC_MIN_BLOCKS, BLOCK, 0, st>>>(s, j, it & 1);
+        *launches += 1;
+    }
     const bool lens = cam.lens_radius > 0.0f;
     const int q = it & 1;
     static const int tb = getenv("HRT_TRACE_BUILD") ? atoi(getenv("HRT_TRACE_BUILD")) : 0;      // A/B: 4 = 128-register build, 8 = 64-register build
     if (s.big_mesh || force_wtrace) {
         const int blocks = wave2_trace_blocks(j.capacity, sm_count, HRT_WTRACE_MIN_BLOCKS);
         if (lens) k_wave2_trace<HRT_WTRACE_MIN_BLOCKS, true, true><<<blocks, BLOCK, 0, st>>>(s, j, cam, q, wsec);
-        else k_wave2_trace<HRT_WTRACE_MIN_BLOCKS, false, true><<<blocks, BLOCK, 0, st>>>(s, j, cam, q, wsec);
+        else if (s.wide_has_slow) k_wave2_trace<HRT_WTRACE_MIN_BLOCKS, false, true, true><<<blocks, BLOCK, 0, st>>>(s, j, cam, q, wsec);
+        else k_wave2_trace<HRT_WTRACE_MIN_BLOCKS, false, true, false><<<blocks, BLOCK, 0, st>>>(s, j, cam, q, wsec);
     } else if (tb ? tb == 8 : secondary_heavy) {
         if (lens) k_wave2_trace<8, true, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, q, wsec);
         else k_wave2_trace<8, false, false><<<wave2_trace_blocks(j.capacity, sm_count, 8), BLOCK, 0, st>>>(s, j, cam, q, wsec);

@@ -104,6 +104,7 @@ struct DScene {
     int background;
     int fast;                   // 0: reference visiting order everywhere; 1: SAH BVHs + reference-order re-trace of ambiguous rays
     int big_mesh;               // 1: some mesh has >= 2^17 triangles (its trees leave L1: the wide walk pays for every ray kind)
+    int wide_has_slow;          // 1: some top-level leaf carries WIDE_SLOW_BIT (an entry that takes the general object test): the kernels with the fifth phase
     int wide_phase_min;         // wide walk: a phase runs when at least this many lanes wait for it (hrt_wide.cuh; 8 with meshes, 16 without)
     int wide_phase_min_obj;     // the same for world-list entries that are tested on the spot (spheres, rects, boxes, media)
     int wide_refill;            // wide walk: idle lanes take new rays as soon as fewer than this many lanes are walking (24)

@@ -65,6 +65,7 @@ DScene make_dscene(HostScene& s, Up& up)
     // r3d A/B (Mrays/s at phase_min 8 / 12 / 16): teapot_scene 2136 / 2138 / 2133, ray batch 1705 / 1529 / 1536, big_mesh 2498 / 2403 / 2398,
     // cornell_smoke 3798 / 4013 / 4342 - without meshes every leaf is a world-list entry and fuller phases pay
     // (r3e, cornell_smoke at phase_min / refill 8/24, 16/24, 16/16, 20/20, 24/24: 3809, 4352, 4705, 4508, 4359; refill 16 costs the mesh scenes 5-10 %)
+    d.wide_has_slow = s.tlas_has_slow ? 1 : 0;
     d.wide_phase_min = meshes.empty() ? 16 : 8; d.wide_phase_min_obj = meshes.empty() ? 16 : 12;   /* r3g teapot_scene at 8/8, 8/12, 8/16, 8/24: 2099, 2127, 2115, 2127; mesh entries keep the node threshold (r3i: ray batch 1722 vs 1554 when they wait for 12) */ d.wide_refill = meshes.empty() ? 16 : 24;
     d.refill_secondary = (fast && (!meshes.empty() || d.n_objects <= 64)) ? 1 : 0;
     d.big_mesh = 0;
